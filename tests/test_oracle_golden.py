@@ -1,0 +1,138 @@
+"""Pin the CPU oracle (oracle/bsrnn_oracle.py) to the reference.
+
+The reference has no tests or golden vectors of its own, so the pin is
+tests/golden/*, produced by oracle/gen_golden.py from the unmodified reference
+bsrnn.py.  When /root/reference is present (build container) the oracle is also
+compared with the imported reference directly.
+"""
+import contextlib
+import io
+import json
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import bsrnn_oracle as O
+
+torch.set_grad_enabled(False)
+TOL = 2e-5   # fp32 CPU, different op order / thread count only
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name))
+
+
+def test_band_table_and_contract(golden_dir):
+    c = json.load(open(os.path.join(golden_dir, "contract.json")))
+    assert O.BAND_WIDTHS == c["bandsplits"] == [1, 2, 3, 6, 12, 24, 48, 96, 192, 384, 257, 0]
+    spec = O.state_dict_spec()
+    assert [[k, list(s)] for k, s, _ in spec] == c["keys"]
+    assert len(spec) == 288
+    assert sum(int(np.prod(s)) for _, s, _ in spec) == c["n_params"] == 7481062
+    assert O.BAND_OFFS == [0, 2, 6, 12, 24, 48, 96, 192, 384, 768, 1536, 2050]
+
+
+def test_weights_are_reproducible(oracle_sd):
+    # MT19937 stream is frozen: a few spot values pin the generator on any box
+    again = O.make_state_dict(0)
+    assert all(torch.equal(oracle_sd[k], again[k]) for k in again)
+    assert float(oracle_sd["bandFCs.11.0.trainable_constant"].abs().sum()) > 0
+
+
+def test_forward_stages_vs_golden(golden_dir, oracle_sd):
+    g = _load(golden_dir, "offline_small.npz")
+    st = O.forward_stages(oracle_sd, torch.from_numpy(g["x"]))
+    for k in ("residual", "feat", "rnn0", "rnn1", "rnn2", "rnn3", "y"):
+        ref = torch.from_numpy(g[k])
+        err = O.max_rel_err(st[k].reshape(ref.shape[0], -1), ref.reshape(ref.shape[0], -1))
+        assert err < TOL, (k, err)
+
+
+def test_forward_recurrent_vs_golden(golden_dir, oracle_sd):
+    g = _load(golden_dir, "recurrent_small.npz")
+    s = torch.from_numpy(g["state0"])
+    for h in range(g["x"].shape[0]):
+        y, s = O.forward_recurrent(oracle_sd, torch.from_numpy(g["x"][h]), s)
+        assert O.max_rel_err(y, torch.from_numpy(g["y"][h])) < TOL
+        assert float((s - torch.from_numpy(g["state"][h])).abs().max()) < TOL
+
+
+def test_wrap_vs_golden(golden_dir):
+    g = _load(golden_dir, "wrap_small.npz")
+    wav = torch.from_numpy(g["wav"])
+    packed = O.stft_pack(wav)
+    assert packed.shape == (2, 2050, 1 + 7000 // 1024)
+    assert O.max_rel_err(packed, torch.from_numpy(g["packed"])) < 1e-6
+    assert O.max_rel_err(O.unpack_istft(packed), torch.from_numpy(g["istft"])) < 1e-6
+    assert O.max_rel_err(O.unpack_istft(torch.from_numpy(g["xr"])), torch.from_numpy(g["istft_r"])) < 1e-6
+
+
+def test_stream_vs_golden(golden_dir, oracle_sd):
+    g = _load(golden_dir, "stream_small.npz")
+    out, state = O.stream(oracle_sd, torch.from_numpy(g["wav"]))
+    assert O.max_rel_err(out, torch.from_numpy(g["out"])) < TOL
+    assert float((state - torch.from_numpy(g["state"])).abs().max()) < TOL
+
+
+def test_cfg1_vs_golden(golden_dir, oracle_sd):
+    g = _load(golden_dir, "cfg1.npz")
+    wav, src = O.synth_audio(1, 176400, seed=1234)
+    wav = torch.cat((wav, wav), 0)
+    x = O.stft_pack(wav)
+    assert list(x.shape) == list(g["shape_x"]) == [2, 2050, 173]
+    y = O.forward(oracle_sd, x)
+    sep = O.unpack_istft(y)
+    assert list(sep.shape) == list(g["shape_out"]) == [2, 176128]
+    assert O.max_rel_err(y[:, ::7, ::5].reshape(2, -1), torch.from_numpy(g["y_dec"]).reshape(2, -1)) < 5e-5
+    assert O.max_rel_err(sep[:, ::37], torch.from_numpy(g["sep_dec"])) < 5e-5
+    sis = O.si_sdr(sep, torch.cat((src, src), 0)[:, :sep.shape[1]]).numpy()
+    assert np.abs(sis - g["si_sdr"]).max() < 1e-3
+
+
+def test_lstm_loop_restatement_matches_aten(oracle_sd):
+    rs = np.random.RandomState(3)
+    x = torch.from_numpy(rs.standard_normal((3, 5, 64)).astype(np.float32))
+    for j in range(4):
+        nd = 2 if j % 2 == 0 else 1
+        st = (torch.from_numpy(rs.standard_normal((2 * nd, 3, 64)).astype(np.float32) * 0.3),
+              torch.from_numpy(rs.standard_normal((2 * nd, 3, 64)).astype(np.float32) * 0.3))
+        a, (h, c) = O.rnn_block(oracle_sd, j, x, st)
+        b, (hn, cn) = O.rnn_block_numpy(oracle_sd, j, x.numpy(), st)
+        assert np.abs(a.numpy() - b).max() < 2e-6
+        assert np.abs(h.numpy() - hn).max() < 2e-6 and np.abs(c.numpy() - cn).max() < 2e-6
+
+
+def test_invariants_recurrent_equals_offline_and_row_independence(oracle_sd):
+    rs = np.random.RandomState(11)
+    x = torch.from_numpy(rs.standard_normal((3, 2050, 5)).astype(np.float32))
+    y = O.forward(oracle_sd, x)
+    s = torch.zeros(4, 2, 36, 64)
+    ys = []
+    for t in range(5):
+        yy, s = O.forward_recurrent(oracle_sd, x[:, :, t].contiguous(), s)
+        ys.append(yy)
+    assert O.max_rel_err(torch.stack(ys, 2), y) < TOL
+    y1 = O.forward(oracle_sd, x[1:2])
+    assert O.max_rel_err(y1, y[1:2]) < 1e-6
+    win = O.hann()
+    assert float((win[:1024] + win[1024:] - 1).abs().max()) < 5e-7
+
+
+@pytest.mark.skipif(not os.path.exists("/root/reference/bsrnn.py"), reason="reference not on this box")
+def test_oracle_vs_imported_reference(oracle_sd):
+    sys.path.insert(0, "/root/reference")
+    with contextlib.redirect_stdout(io.StringIO()):
+        import bsrnn as ref
+        m = ref.BSRNN()
+    m.load_state_dict(oracle_sd, strict=True)
+    m.eval()
+    rs = np.random.RandomState(5)
+    x = torch.from_numpy(rs.standard_normal((2, 2050, 9)).astype(np.float32))
+    assert O.max_rel_err(O.forward(oracle_sd, x), m.forward(x)) < TOL
+    st = torch.from_numpy(rs.standard_normal((4, 2, 24, 64)).astype(np.float32) * 0.2)
+    yr, sr = m.forward_recurrent(x[:, :, 0], st)
+    yo, so = O.forward_recurrent(oracle_sd, x[:, :, 0], st)
+    assert O.max_rel_err(yo, yr) < TOL and float((so - sr).abs().max()) < TOL
