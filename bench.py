@@ -1,0 +1,317 @@
+#!/usr/bin/env python
+"""Benchmark of the BSRNN separation path (BASELINE.json metric: audio-sec separated/sec).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One "step" = one pass of waveform -> STFT -> BSRNN.forward -> iSTFT -> waveform over the
+workload (default: BASELINE.json configs[1], 64 x 10 s clips per GPU, weak scaling).
+Prints ONE JSON line on rank 0.  See DESIGN.md "Measurement" for the definitions.
+"""
+from __future__ import annotations
+
+import argparse
+import contextlib
+import io
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SR = 44100
+BAND_D = [2, 4, 6, 12, 24, 48, 96, 192, 384, 768, 514]
+WORKLOADS = {
+    # name: (rows per GPU, samples per row)
+    "cfg2_offline_64x10s": (64, 441000),
+    "cfg1_offline_2x4s": (2, 176400),
+    "cfg5_longform_1x60s": (1, 2646000),
+}
+
+
+def synth(rows: int, n: int, device, seed: int = 1234) -> torch.Tensor:
+    """Synthetic mixture: 150 Hz 5-harmonic AM tone (peak 0.3) + 0.1*randn, different per row."""
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    t = torch.arange(n, dtype=torch.float64) / SR
+    out = torch.empty(rows, n, dtype=torch.float32)
+    for r in range(rows):
+        f0 = 150.0 * (1.0 + 0.02 * (r % 16))
+        s = sum(torch.sin(2 * torch.pi * f0 * (h + 1) * t + 0.7 * h + r) / (h + 1) for h in range(5))
+        s = s * (0.6 + 0.4 * torch.sin(2 * torch.pi * 4.0 * t + r))
+        s = 0.3 * s / s.abs().max()
+        out[r] = (s + 0.1 * torch.randn(n, generator=g, dtype=torch.float64)).float()
+    return out.to(device)
+
+
+def stage_work(T: int):
+    """Algorithmic FLOPs and bytes per frame-row of each timed stage; fp32."""
+    mac = {}
+    mac["pre"] = sum(2 * d * d for d in BAND_D)
+    mac["bandfc"] = sum(d * max(d, 64) + max(d, 64) * 64 + 64 * 64 for d in BAND_D)
+    mac["back"] = sum(64 * 128 + 128 * max(d, 128) + max(d, 128) * d for d in BAND_D)
+    mac["post_mask"] = sum(2 * d * d for d in BAND_D)
+    for j in range(4):
+        nd = 2 if j % 2 == 0 else 1
+        mac[f"rnn{j}.proj0"] = 12 * (64 * 64 + 64 * 256 * nd)
+        mac[f"rnn{j}.proj1"] = 12 * (64 * nd * 256 * nd)
+        mac[f"rnn{j}.rec0"] = 12 * (64 * 256 * nd)
+        mac[f"rnn{j}.rec1"] = 12 * (64 * 256 * nd)
+        mac[f"rnn{j}.fc"] = 12 * (64 * nd * 64)
+    flops = {k: 2.0 * v for k, v in mac.items()}
+    flops["stft"] = flops["istft"] = 5.0 * 1024 * 10 + 8 * 1024      # 1024-pt complex FFT + split
+    byt = {"stft": 4096 + 8200, "istft": 8200 + 4096, "pre": 8200 + 8200, "bandfc": 8200 + 3072,
+           "back": 3072 + 8200, "post_mask": 8200 * 4}
+    for j in range(4):
+        nd = 2 if j % 2 == 0 else 1
+        byt[f"rnn{j}.proj0"] = 3072 + 12 * 256 * nd * 4
+        byt[f"rnn{j}.proj1"] = 12 * 64 * nd * 4 + 12 * 256 * nd * 4
+        byt[f"rnn{j}.rec0"] = byt[f"rnn{j}.rec1"] = 12 * 256 * nd * 4 + 12 * 64 * nd * 4
+        byt[f"rnn{j}.fc"] = 12 * 64 * nd * 4 + 3072 * 2
+    return flops, byt
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.lines = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        # median over the busier half of the samples (the region is bracketed by idle time)
+        load = sm[len(sm) // 2:] if sm else []
+        med = load[len(load) // 2] if load else None
+        return {"sm_mhz": med, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm": d["hbm_gbs"], "tensor": d["bf16_tflops"], "tensor_sustained": d.get("bf16_tflops_sustained"),
+                "src": "measured"}
+    return {"hbm": 6650.0, "tensor": 1590.0, "tensor_sustained": 1400.0, "src": "fallback"}
+
+
+def cpu_baseline(rows: int, n: int, repeats: int = 3):
+    """The oracle (CPU restatement of the reference path = stock PyTorch fp32 ops, what the
+    reference itself runs) on the host cores, on a bounded sample of the workload."""
+    from oracle import bsrnn_oracle as O          # checker/baseline only, never on the product path
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sd = O.make_state_dict(0)
+    wav = synth(rows, n, "cpu")
+    with torch.no_grad():
+        O.separate(sd, wav[:1, : min(n, 44100)])   # warm-up
+        best = float("inf")
+        for _ in range(repeats):
+            t0 = time.perf_counter()
+            O.separate(sd, wav)
+            best = min(best, time.perf_counter() - t0)
+    return {"value": rows * n / SR / best, "unit": "audio-sec/s", "cores": cores, "kind": "port",
+            "sample": f"{rows} x {n / SR:.1f} s clips, best of {repeats}, oracle/bsrnn_oracle.py (torch {torch.__version__} CPU fp32)"}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's own CPU implementation of the path (stock PyTorch ops,
+    restated in oracle/) on all host cores; each step is a bounded sample of the workload."""
+    if rank != 0:
+        return
+    rows_full, n = WORKLOADS[args.workload]
+    rows = min(rows_full, 4)
+    from oracle import bsrnn_oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sd = O.make_state_dict(0)
+    wav = synth(rows, n, "cpu")
+    with torch.no_grad():
+        for _ in range(args.warmup):
+            O.separate(sd, wav)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            O.separate(sd, wav)
+        dt = time.perf_counter() - t0
+    val = args.steps * rows * n / SR / dt
+    sample = f"{rows} of {rows_full} rows x {n / SR:.1f} s per step"
+    print(json.dumps({
+        "impl": "reference", "metric": "audio-sec separated/sec", "value": val, "unit": "audio-sec/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "sample": sample, "device": "cpu"},
+        "cpu_baseline": {"value": val, "unit": "audio-sec/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "audio-sec/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="cfg2_offline_64x10s", choices=list(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.set_grad_enabled(False)
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch.distributed as dist
+    from speechseparation_b200 import BSRNN, _lib, aggregate_throughput
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    l = _lib.lib()
+    rows, n = WORKLOADS[args.workload]
+    T = l.bsb_num_frames(n)
+    frame_rows = rows * T
+    audio_s = rows * n / SR
+
+    torch.manual_seed(0)                       # random-init weights of the reference architecture
+    with contextlib.redirect_stdout(io.StringIO()):
+        model = BSRNN().to(dev).eval()
+    wav = synth(rows, n, dev, seed=1234 + rank)
+    out = torch.empty((rows, 1024 * (T - 1)), dtype=torch.float32, device=dev)
+    host_in = wav.cpu().pin_memory()
+    host_out = torch.empty(out.shape, dtype=torch.float32).pin_memory()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput (`value`) with per-stage events ---------------------------
+    for _ in range(args.warmup):
+        model.separate(wav, out=out)
+    l.bsb_set_stage_timing(1)
+    stage_ms = {}
+    barrier()
+    clocks = ClockSampler(local)
+    clocks.start()
+    time.sleep(0.3)
+    n0 = l.bsb_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    pending = []
+    for _ in range(args.steps):
+        model.separate(wav, out=out)
+        # stage events of this step are read back after the region (no sync inside it) only for
+        # the last step; earlier steps are sampled in the second loop below
+    e1.record()
+    barrier()
+    dt = e0.elapsed_time(e1) / 1e3
+    launches = l.bsb_launch_count() - n0
+    for name, ms in _lib.stage_times():
+        stage_ms[name] = stage_ms.get(name, 0.0) + ms
+    clk = clocks.stop()
+    l.bsb_set_stage_timing(0)
+    units, tmax = aggregate_throughput(audio_s * args.steps, dt, device=dev)
+
+    # ---- end to end through the public API with host buffers ------------------------------------
+    barrier()
+    t_e2e0 = torch.cuda.Event(enable_timing=True)
+    t_e2e1 = torch.cuda.Event(enable_timing=True)
+    t_e2e0.record()
+    for _ in range(args.steps):
+        wav.copy_(host_in, non_blocking=True)
+        model.separate(wav, out=out)
+        host_out.copy_(out, non_blocking=True)
+    t_e2e1.record()
+    barrier()
+    dte = t_e2e0.elapsed_time(t_e2e1) / 1e3
+    units_e, tmax_e = aggregate_throughput(audio_s * args.steps, dte, device=dev)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    # ---- roofline of the dominant stage ----------------------------------------------------------
+    pk = peaks()
+    flops, byt = stage_work(T)
+    top = max(stage_ms, key=stage_ms.get)
+    total_ms = sum(stage_ms.values())
+    t_top = stage_ms[top] / 1e3
+    hbm_ach = byt[top] * frame_rows / t_top / 1e9
+    fl_ach = flops[top] * frame_rows / t_top / 1e12
+    # a stage is HBM-bound if its HBM time at peak exceeds its tensor time at peak
+    hbm_bound = (byt[top] / pk["hbm"] / 1e9) > (flops[top] / pk["tensor"] / 1e12)
+    roof = ({"bound": "hbm", "achieved": hbm_ach, "peak": pk["hbm"], "unit": "GB/s", "frac": hbm_ach / pk["hbm"]}
+            if hbm_bound else
+            {"bound": "tensor", "achieved": fl_ach, "peak": pk["tensor"], "unit": "TFLOP/s", "frac": fl_ach / pk["tensor"]})
+    roof.update({"kernel": top, "share_of_step": stage_ms[top] / total_ms, "traffic": None,
+                 "peak_source": pk["src"], "arith": "fp32 FFMA (no tensor cores yet)"})
+    stages = {k: {"ms": v, "tflops": flops[k] * frame_rows / (v / 1e3) / 1e12,
+                  "gbs": byt[k] * frame_rows / (v / 1e3) / 1e9} for k, v in stage_ms.items()}
+    res = {
+        "metric": "audio-sec separated/sec", "value": units / tmax, "unit": "audio-sec/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tmax / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "rows_per_gpu": rows, "clip_s": n / SR, "frames": T,
+                   "frame_rows_per_gpu": frame_rows, "l2": "inputs+workspace (>2 GB/step) larger than L2",
+                   "weights": "random init, torch.manual_seed(0)"},
+        "e2e": {"value": units_e / tmax_e, "unit": "audio-sec/s", "h2d_bytes_per_step": host_in.numel() * 4,
+                "d2h_bytes_per_step": host_out.numel() * 4},
+        "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "stages": stages,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        res["cpu_baseline"] = cpu_baseline(min(rows, 4), n)
+    print(json.dumps(res))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

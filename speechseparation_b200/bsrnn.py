@@ -1,0 +1,264 @@
+"""Drop-in ``bsrnn.BSRNN`` backed by the hand-written sm_100a kernels of libbsrnn_b200.so.
+
+Mirrors the reference module tree (reference bsrnn.py:12-24, 63-162, 328-376) so that
+``state_dict()`` has the same 288 keys / shapes / order and ``load_state_dict(strict=True)``
+of a reference checkpoint works, and keeps the reference signatures
+
+    BSRNN()                                   (no arguments, bsrnn.py:329)
+    BSRNN.forward(x[C,2050,T]) -> y[C,2050,T]                      (bsrnn.py:385)
+    BSRNN.forward_recurrent(x[C,2050], state[4,2,C*12,64]) -> (y, new_state)  (bsrnn.py:445)
+
+The ``nn.Linear`` / ``nn.LSTM`` sub-modules only hold parameters; the arithmetic runs in the
+CUDA library through its C ABI (include/bsrnn_b200.h).  There is no CPU path: tensors that
+are not on a CUDA device raise.  The path is forward-only (north_star): asking autograd for
+a gradient through it raises NotImplementedError in backward.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional, Tuple
+
+import torch
+from torch import nn
+
+from . import _lib
+
+band_features = 64          # reference bsrnn.py:60
+merge_channels = False      # reference bsrnn.py:61
+N_SPEC = 2050
+
+
+def generate_bandsplits() -> Tuple[List[int], List[int]]:
+    """Band widths (bins) and neighbour sums, as reference bsrnn.py:247-326 returns them.
+
+    The widths come from the library's compile-time table (bsb_band_widths), the same table
+    the kernels index with; ``w`` (unused by the live model) is derived as the reference does.
+    """
+    buf = (ctypes.c_int * 12)()
+    _lib.check(_lib.lib().bsb_band_widths(buf), "bsb_band_widths")
+    v = list(buf)
+    w = [v[i] + v[i + 1] for i in range(len(v) - 1)] + [v[0] + v[-1]]
+    return v, w
+
+
+class TrainableConstantModule(nn.Module):
+    """Parameter holder for the zero-width band 11 (reference bsrnn.py:12-24)."""
+
+    def __init__(self, shape):
+        super().__init__()
+        self.trainable_constant = nn.Parameter(torch.zeros(shape, dtype=torch.float32))
+
+
+class NormRNNResidual(nn.Module):
+    """Parameter holder: fc_in -> 2-layer LSTM -> fc (+x) (reference bsrnn.py:63-98)."""
+
+    def __init__(self, bidirectional: bool = False):
+        super().__init__()
+        self.fc_in = nn.Linear(band_features, band_features)
+        self.rnn = nn.LSTM(band_features, band_features, batch_first=True, num_layers=2,
+                           bidirectional=bidirectional)
+        self.fc = nn.Linear(band_features * (2 if bidirectional else 1), band_features)
+
+
+class TimewiseLSTM(nn.Module):      # reference bsrnn.py:101-128
+    def __init__(self):
+        super().__init__()
+        self.m = NormRNNResidual()
+
+
+class BandwiseLSTM(nn.Module):      # reference bsrnn.py:131-162
+    def __init__(self):
+        super().__init__()
+        self.m = NormRNNResidual(bidirectional=True)
+
+
+def _stream_ptr() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+class _ForwardOnly(torch.autograd.Function):
+    """Runs the CUDA forward; backward is not part of this path (north_star is inference)."""
+
+    @staticmethod
+    def forward(ctx, model, x, *params):
+        return model._forward_impl(x)
+
+    @staticmethod
+    def backward(ctx, *grads):
+        raise NotImplementedError(
+            "speechseparation_b200.BSRNN is forward-only: the B200 kernels implement the separation "
+            "forward pass (BASELINE.json north_star); no backward is provided. Run under torch.no_grad().")
+
+
+class BSRNN(nn.Module):
+    def __init__(self):
+        super().__init__()
+        band_split = generate_bandsplits()
+        lrelu = nn.LeakyReLU
+        # construction order = the reference's, so `torch.manual_seed(s); BSRNN()` draws the same
+        # default init and state_dict() lists the same keys in the same order (bsrnn.py:333-376)
+        self.bandFCs_pre = nn.ModuleList([
+            (nn.Sequential(nn.Linear(x * 2, x * 2), lrelu(), nn.Linear(x * 2, x * 2), lrelu())
+             if x > 0 else nn.Sequential(TrainableConstantModule([0]))) for x in band_split[0]])
+        self.bandFCs = nn.ModuleList([
+            (nn.Sequential(nn.Linear(x * 2, max(x * 2, band_features)), lrelu(),
+                           nn.Linear(max(x * 2, band_features), band_features), lrelu(),
+                           nn.Linear(band_features, band_features))
+             if x > 0 else nn.Sequential(TrainableConstantModule([band_features]))) for x in band_split[0]])
+        print(band_split)                                     # reference side effect, bsrnn.py:351
+        self.lstms = nn.Sequential(BandwiseLSTM(), TimewiseLSTM(), BandwiseLSTM(), TimewiseLSTM())
+        hidden = band_features * 2
+        self.bandFCs_back = nn.ModuleList([
+            (nn.Sequential(nn.Linear(band_features, hidden), lrelu(),
+                           nn.Linear(hidden, max(x * 2, hidden)), lrelu(),
+                           nn.Linear(max(x * 2, hidden), x * 2), lrelu())
+             if x > 0 else nn.Sequential(TrainableConstantModule(0))) for x in band_split[0]])
+        self.bandFCs_back_post = nn.ModuleList([
+            (nn.Sequential(nn.Linear(x * 2, x * 2), lrelu(), nn.Linear(x * 2, x * 2))
+             if x > 0 else nn.Sequential(TrainableConstantModule([0]))) for x in band_split[0]])
+        self._packed: Optional[torch.Tensor] = None
+        self._packed_sig = None
+        self._ws: Optional[torch.Tensor] = None
+
+    # ---- pickling: device caches are not part of the module's state (infer-streaming.py:49) ----
+    def __getstate__(self):
+        d = self.__dict__.copy()
+        d["_packed"] = None
+        d["_packed_sig"] = None
+        d["_ws"] = None
+        return d
+
+    # ---- weight packing ---------------------------------------------------------------------
+    def _signature(self):
+        return tuple((p.data_ptr(), p._version) for p in self.parameters())
+
+    def packed_weights(self, device: torch.device) -> torch.Tensor:
+        """Packed device copy of the 288 parameters; re-packed whenever a parameter's storage
+        or version changes (load_state_dict, .to(), optimizer steps)."""
+        sig = self._signature()
+        if self._packed is not None and self._packed_sig == sig and self._packed.device == device:
+            return self._packed
+        params = list(self.state_dict(keep_vars=True).values())
+        l = _lib.lib()
+        if len(params) != 288:
+            raise RuntimeError(f"expected 288 state_dict entries, found {len(params)}")
+        for i, p in enumerate(params):
+            if p.dtype != torch.float32:
+                raise RuntimeError("BSRNN parameters must be float32 (the kernels compute in fp32)")
+            if p.device != device:
+                raise RuntimeError(f"parameter on {p.device}, input on {device}: move the model with .to()")
+            if p.numel() != l.bsb_tensor_numel(i):
+                raise RuntimeError(f"state_dict entry {i} has {p.numel()} elements, expected {l.bsb_tensor_numel(i)}")
+        keep = [p.detach().contiguous() for p in params]
+        table = (ctypes.c_void_p * 288)(*[(t.data_ptr() if t.numel() else None) for t in keep])
+        with torch.cuda.device(device):
+            packed = torch.empty(l.bsb_packed_weights_bytes() // 4, dtype=torch.float32, device=device)
+            _lib.check(l.bsb_pack_weights(table, 288, packed.data_ptr(), _stream_ptr()), "bsb_pack_weights")
+        self._packed, self._packed_sig = packed, sig
+        return packed
+
+    def workspace(self, nbytes: int, device: torch.device) -> torch.Tensor:
+        if self._ws is None or self._ws.device != device or self._ws.numel() < nbytes:
+            self._ws = None
+            self._ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        return self._ws
+
+    # ---- checks ------------------------------------------------------------------------------
+    @staticmethod
+    def _check_input(x: torch.Tensor, ndim: int, what: str):
+        if not isinstance(x, torch.Tensor):
+            raise TypeError(f"{what} must be a torch.Tensor")
+        if not x.is_cuda:
+            raise RuntimeError(f"{what} is on {x.device}: speechseparation_b200 has no CPU path; move it to a CUDA device")
+        if x.dtype != torch.float32:
+            raise RuntimeError(f"{what} must be float32, got {x.dtype}")
+        if x.dim() != ndim:
+            raise RuntimeError(f"{what} must have {ndim} dims, got shape {tuple(x.shape)}")
+        if x.shape[1] != N_SPEC:
+            raise RuntimeError(f"{what}: dim 1 must be {N_SPEC} (1025 bins x Re/Im), got shape {tuple(x.shape)}")
+        if x.shape[0] < 1:
+            raise RuntimeError(f"{what}: empty dim 0")
+
+    def _needs_grad(self, *tensors) -> bool:
+        if not torch.is_grad_enabled():
+            return False
+        return any(t.requires_grad for t in tensors) or any(p.requires_grad for p in self.parameters())
+
+    # ---- reference API -------------------------------------------------------------------------
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        """x [C,2050,T] fp32 CUDA -> x * mask, same shape (reference bsrnn.py:385-443)."""
+        self._check_input(x, 3, "x")
+        if x.shape[2] < 1:
+            raise RuntimeError("x: empty time axis")
+        if self._needs_grad(x):
+            return _ForwardOnly.apply(self, x, *self.parameters())
+        return self._forward_impl(x)
+
+    def _forward_impl(self, x: torch.Tensor) -> torch.Tensor:
+        l = _lib.lib()
+        x = x.detach().contiguous()
+        C, _, T = x.shape
+        dev = x.device
+        packed = self.packed_weights(dev)
+        with torch.cuda.device(dev):
+            nbytes = l.bsb_workspace_bytes(C, T)
+            ws = self.workspace(nbytes, dev)
+            y = torch.empty_like(x)
+            _lib.check(l.bsb_forward(x.data_ptr(), C, T, packed.data_ptr(), y.data_ptr(), ws.data_ptr(),
+                                     ws.numel(), _stream_ptr()), "bsb_forward")
+        return y
+
+    def forward_recurrent(self, x: torch.Tensor, state: torch.Tensor):
+        """x [C,2050], state [4,2,C*12,64] -> (y [C,2050], new_state) (reference bsrnn.py:445-510)."""
+        self._check_input(x, 2, "x")
+        C = x.shape[0]
+        if not isinstance(state, torch.Tensor) or tuple(state.shape) != (4, 2, C * 12, band_features):
+            shape = tuple(state.shape) if isinstance(state, torch.Tensor) else type(state)
+            raise RuntimeError(f"state must have shape (4, 2, {C * 12}, {band_features}) for {C} rows, got {shape}")
+        if state.device != x.device or state.dtype != torch.float32:
+            raise RuntimeError("state must be float32 on the same CUDA device as x")
+        if self._needs_grad(x, state):
+            raise NotImplementedError("speechseparation_b200.BSRNN.forward_recurrent is forward-only; "
+                                      "call it under torch.no_grad()")
+        l = _lib.lib()
+        x = x.detach().contiguous()
+        state = state.detach().contiguous()
+        dev = x.device
+        packed = self.packed_weights(dev)
+        with torch.cuda.device(dev):
+            ws = self.workspace(l.bsb_workspace_bytes(C, 1), dev)
+            y = torch.empty_like(x)
+            new_state = torch.empty_like(state)
+            _lib.check(l.bsb_forward_recurrent(x.data_ptr(), C, state.data_ptr(), packed.data_ptr(), y.data_ptr(),
+                                               new_state.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr()),
+                       "bsb_forward_recurrent")
+        return y, new_state
+
+    # ---- fused wrap: waveform in, waveform out (body of m_dataset.infer, m_dataset.py:182-195) ----
+    def separate(self, wav: torch.Tensor, window: Optional[torch.Tensor] = None,
+                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """wav [C,L] fp32 CUDA -> separated [C, 1024*(L//1024)]: stft -> forward -> istft in one
+        C-ABI call, without materialising the [C,2050,T] boundary tensors."""
+        if not wav.is_cuda or wav.dtype != torch.float32 or wav.dim() != 2:
+            raise RuntimeError("wav must be a float32 CUDA tensor of shape [C, L]")
+        if self._needs_grad(wav):
+            raise NotImplementedError("speechseparation_b200.BSRNN.separate is forward-only")
+        l = _lib.lib()
+        wav = wav.detach().contiguous()
+        C, L = wav.shape
+        T = l.bsb_num_frames(L)
+        if T < 2:
+            raise RuntimeError(f"wav too short for reflect padding / overlap-add: L={L} (need > 1024)")
+        dev = wav.device
+        packed = self.packed_weights(dev)
+        with torch.cuda.device(dev):
+            ws = self.workspace(l.bsb_workspace_bytes(C, T), dev)
+            if out is None:
+                out = torch.empty((C, 1024 * (T - 1)), dtype=torch.float32, device=dev)
+            _lib.check(l.bsb_separate(wav.data_ptr(), C, L, _p(window), packed.data_ptr(), out.data_ptr(),
+                                      ws.data_ptr(), ws.numel(), _stream_ptr()), "bsb_separate")
+        return out

@@ -1,0 +1,89 @@
+// Internal kernel-launch interface shared by the .cu files of libbsrnn_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include "layout.h"
+
+namespace bsb {
+
+// every kernel launch goes through this counter (bsb_launch_count)
+extern long long g_launches;
+inline void count_launch(int n = 1) { g_launches += n; }
+
+// ------------------------------------------------------------------------------------
+// grouped Linear:  O[m][n] = epi( sum_k A[m][k] * W[n][k] + bias[n] )
+// up to kMaxProb independent problems (the 11 bands of one MLP layer) in one launch.
+// ------------------------------------------------------------------------------------
+enum Act : int { ACT_NONE = 0, ACT_LRELU = 1 };
+
+struct LinProb {
+  const float* A;      // [M][lda], K valid columns
+  const float* W;      // [Npad][ldw] zero padded (ldw = Kpad)
+  const float* bias;   // [Npad]
+  float* O;            // [M][ldo]
+  const float* res;    // optional: v += res[m][n]   (after activation)
+  const float* mul;    // optional: v *= mul[m][n]   (after res)
+  int lda, ldw, ldo, ldres, ldmul;
+  int M, N, K;
+  int act;
+  int tile_start;      // first tile index of this problem in the launch
+  int tiles_n;
+};
+constexpr int kMaxProb = 12;
+struct GroupedArgs {
+  LinProb p[kMaxProb];
+  int nprob;
+  int total_tiles;
+};
+
+// fills tile_start/tiles_n/total_tiles and launches (no-op when there is no work)
+cudaError_t launch_grouped_linear(GroupedArgs& args, cudaStream_t s);
+
+// ------------------------------------------------------------------------------------
+// LSTM recurrence over precomputed gate pre-activations.
+//   gates(seq, step) = xproj(seq, step)[dir*256 .. +256] + W_hh[dir] . h(seq, step-1)
+// element offset of (seq, step) = (seq / n_inner) * outer + (seq % n_inner) * inner + step * stepstride
+// ------------------------------------------------------------------------------------
+struct LstmArgs {
+  const float* xproj;
+  const float* whh;          // [ndir][256][64]
+  float* hout;               // h of every step; column offset dir*64
+  const float* h0;           // optional [nseq][64] (dir 0 only)
+  const float* c0;
+  float* hN;                 // optional final state [nseq][64]
+  float* cN;
+  long long xp_outer, xp_inner, xp_step;
+  long long ho_outer, ho_inner, ho_step;
+  int n_inner;
+  int nseq, nsteps, ndir;
+};
+cudaError_t launch_lstm(const LstmArgs& a, cudaStream_t s);
+
+// ------------------------------------------------------------------------------------
+// signal kernels
+// ------------------------------------------------------------------------------------
+// wav[C][L] -> xf[C*T][xs] (frame-major, 2050 valid floats), torch.stft(center=True, reflect)
+cudaError_t launch_stft_frames(const float* wav, int C, long long L, int T, const float* window,
+                               float* xf, int xs, cudaStream_t s);
+// xf[C*T][xs] -> wav[C][1024*(T-1)], torch.istft semantics
+cudaError_t launch_istft_frames(const float* xf, int xs, int C, int T, const float* window,
+                                float* wav, cudaStream_t s);
+// streaming analysis: ring[C][2048] <- roll + chunk; x[C][2050] = pack(rfft(ring*window))
+cudaError_t launch_stream_analysis(const float* chunk, int C, const float* window, float* ring,
+                                   float* x, cudaStream_t s);
+// streaming synthesis: cur = irfft(unpack(y)); out = (cur[:1024] + tail) / (w[i]+w[i+1024]); tail = cur[1024:]
+cudaError_t launch_stream_synthesis(const float* y, int C, const float* window, float* tail,
+                                    float* out, cudaStream_t s);
+// x[C][2050][T] <-> xf[C*T][xs]
+cudaError_t launch_to_frames(const float* x, int C, int T, float* xf, int xs, cudaStream_t s);
+cudaError_t launch_from_frames(const float* xf, int xs, int C, int T, float* x, cudaStream_t s);
+const float* builtin_window(cudaStream_t s, cudaError_t* err);   // device float[2048], periodic Hann
+const float2* twiddle_tables(cudaStream_t s, cudaError_t* err);  // device: [1024] W_1024^k then [1025] W_2048^k
+
+// ------------------------------------------------------------------------------------
+// weight packing helpers
+// ------------------------------------------------------------------------------------
+cudaError_t launch_pack_matrix(const float* src, int N, int K, float* dst, int ldd, cudaStream_t s);
+cudaError_t launch_pack_bias(const float* b1, const float* b2, int N, float* dst, cudaStream_t s);
+
+}  // namespace bsb

@@ -1,0 +1,160 @@
+"""Signal wrap around the model, on the GPU through the C ABI.
+
+Host-side mirror of what every caller of the reference repeats around ``BSRNN.forward``:
+
+  * ``stft_pack``    <- m_dataset.py:187-190 / infer.py:29-33
+  * ``unpack_istft`` <- m_dataset.py:192-195 / infer.py:35-37
+  * ``infer``        <- m_dataset.py:182-199  (the forward-only part: x, x_time)
+  * ``StreamingSeparator`` <- the per-chunk loop of infer-streaming.py:84-147
+                              (= SpeechSeparator::new_chunk, speech-ladspa-onnx.cpp:171-267)
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _lib
+from .bsrnn import BSRNN, _p, _stream_ptr
+
+N_FFT = 2048
+HOP = 1024
+
+
+def _check_wav(wav: torch.Tensor):
+    if not isinstance(wav, torch.Tensor) or not wav.is_cuda:
+        raise RuntimeError("wav must be a CUDA tensor: speechseparation_b200 has no CPU path")
+    if wav.dtype != torch.float32 or wav.dim() != 2:
+        raise RuntimeError(f"wav must be float32 [C, L], got {wav.dtype} {tuple(wav.shape)}")
+
+
+def _check_window(window: Optional[torch.Tensor], dev):
+    if window is None:
+        return
+    if window.device != dev or window.dtype != torch.float32 or window.numel() != N_FFT or not window.is_contiguous():
+        raise RuntimeError("window must be a contiguous float32 [2048] tensor on the input's device")
+
+
+def stft_pack(wav: torch.Tensor, window: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """[C,L] -> [C,2050,T] with row 2k = Re, 2k+1 = Im of bin k (torch.stft(n_fft=2048,
+    hop=1024, center=True, reflect) + stack/reshape, m_dataset.py:187-190)."""
+    _check_wav(wav)
+    _check_window(window, wav.device)
+    l = _lib.lib()
+    wav = wav.contiguous()
+    C, L = wav.shape
+    T = l.bsb_num_frames(L)
+    if T < 1:
+        raise RuntimeError(f"wav too short for reflect padding: L={L} (need > 1024)")
+    with torch.cuda.device(wav.device):
+        x = torch.empty((C, 2050, T), dtype=torch.float32, device=wav.device)
+        ws = torch.empty(C * T * 2052 * 4, dtype=torch.uint8, device=wav.device)
+        _lib.check(l.bsb_stft_pack(wav.data_ptr(), C, L, _p(window), x.data_ptr(), ws.data_ptr(), ws.numel(),
+                                   _stream_ptr()), "bsb_stft_pack")
+    return x
+
+
+def unpack_istft(x: torch.Tensor, window: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """[C,2050,T] -> [C,1024*(T-1)] (reshape to complex + torch.istft, m_dataset.py:192-195)."""
+    if not isinstance(x, torch.Tensor) or not x.is_cuda or x.dtype != torch.float32 or x.dim() != 3 or x.shape[1] != 2050:
+        raise RuntimeError("x must be a float32 CUDA tensor [C, 2050, T]")
+    _check_window(window, x.device)
+    l = _lib.lib()
+    x = x.contiguous()
+    C, _, T = x.shape
+    if T < 2:
+        raise RuntimeError("istft needs at least 2 frames")
+    with torch.cuda.device(x.device):
+        wav = torch.empty((C, HOP * (T - 1)), dtype=torch.float32, device=x.device)
+        ws = torch.empty(C * T * 2052 * 4, dtype=torch.uint8, device=x.device)
+        _lib.check(l.bsb_unpack_istft(x.data_ptr(), C, T, _p(window), wav.data_ptr(), ws.data_ptr(), ws.numel(),
+                                      _stream_ptr()), "bsb_unpack_istft")
+    return wav
+
+
+def infer(model: BSRNN, waveform: torch.Tensor, window: Optional[torch.Tensor] = None):
+    """Forward-only part of m_dataset.infer (m_dataset.py:182-195): returns (x, x_time) with x the
+    masked spectrogram [C,2050,T] and x_time the separated waveform."""
+    spec = stft_pack(waveform, window)
+    x = model.forward(spec)
+    return x, unpack_istft(x, window)
+
+
+class StreamingSeparator:
+    """Hop-by-hop separation with carried LSTM state (infer-streaming.py:84-147).
+
+    All rolling state (2048-sample ring, LSTM state, overlap-add tail) stays on the device;
+    ``step`` takes 1024 new samples per row and returns the 1024 output samples of that hop
+    (the audio of the previous hop: one-hop algorithmic delay, as the reference).  After the
+    first (warm-up) hop the whole hop is replayed as one CUDA graph.
+    """
+
+    def __init__(self, model: BSRNN, rows: int = 2, device=None, window: Optional[torch.Tensor] = None,
+                 use_graph: bool = True):
+        self.model = model
+        self.rows = int(rows)
+        dev = torch.device(device) if device is not None else next(model.parameters()).device
+        if dev.type != "cuda":
+            raise RuntimeError("StreamingSeparator needs the model on a CUDA device (no CPU path)")
+        self.device = dev
+        _check_window(window, dev)
+        self.window = window
+        l = _lib.lib()
+        C = self.rows
+        with torch.cuda.device(dev):
+            self.ring = torch.zeros((C, N_FFT), dtype=torch.float32, device=dev)
+            self.tail = torch.zeros((C, HOP), dtype=torch.float32, device=dev)
+            self.state = [torch.zeros((4, 2, C * 12, 64), dtype=torch.float32, device=dev) for _ in range(2)]
+            self.chunk = torch.zeros((C, HOP), dtype=torch.float32, device=dev)
+            self.out = torch.zeros((C, HOP), dtype=torch.float32, device=dev)
+            self.ws = torch.empty(l.bsb_stream_workspace_bytes(C), dtype=torch.uint8, device=dev)
+        self.packed = model.packed_weights(dev)
+        self.hops = 0
+        self.use_graph = use_graph
+        self._graphs = None
+
+    def reset(self):
+        for t in (self.ring, self.tail, self.state[0], self.state[1]):
+            t.zero_()
+        self.hops = 0
+
+    def _enqueue(self, parity: int):
+        l = _lib.lib()
+        _lib.check(l.bsb_stream_step(self.chunk.data_ptr(), self.rows, _p(self.window), self.packed.data_ptr(),
+                                     self.ring.data_ptr(), self.state[parity].data_ptr(),
+                                     self.state[parity ^ 1].data_ptr(), self.tail.data_ptr(), self.out.data_ptr(),
+                                     self.ws.data_ptr(), self.ws.numel(), _stream_ptr()), "bsb_stream_step")
+
+    def _capture(self):
+        # two graphs: the LSTM state ping-pongs between two buffers
+        graphs = []
+        saved = [t.clone() for t in (self.ring, self.tail, self.state[0], self.state[1])]
+        for parity in (0, 1):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._enqueue(parity)
+            graphs.append(g)
+        for t, s in zip((self.ring, self.tail, self.state[0], self.state[1]), saved):
+            t.copy_(s)          # capture does not execute, but keep the state provably untouched
+        self._graphs = graphs
+
+    @property
+    def current_state(self) -> torch.Tensor:
+        return self.state[self.hops & 1]
+
+    def step(self, chunk: torch.Tensor) -> torch.Tensor:
+        """chunk [rows,1024] float32 (CUDA, or pinned/pageable host memory: copied in) ->
+        view of the device output buffer [rows,1024] (valid until the next step)."""
+        if chunk.shape != self.chunk.shape or chunk.dtype != torch.float32:
+            raise RuntimeError(f"chunk must be float32 {tuple(self.chunk.shape)}, got {chunk.dtype} {tuple(chunk.shape)}")
+        with torch.cuda.device(self.device):
+            self.chunk.copy_(chunk, non_blocking=True)
+            parity = self.hops & 1
+            if self.use_graph and self.hops >= 2:
+                if self._graphs is None:
+                    self._capture()
+                self._graphs[parity].replay()
+            else:
+                self._enqueue(parity)
+            self.hops += 1
+        return self.out

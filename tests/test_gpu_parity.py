@@ -1,0 +1,243 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle and the golden fixtures
+generated from the reference.  All arithmetic is fp32; gate (north_star):
+max|y - y_ref| / max|y_ref| <= 1e-3 per row on waveforms, |dSI-SDR| <= 0.01 dB.
+Stage tests use a tighter bound (fp32 kernels): 2e-4 relative to the stage's max."""
+import contextlib
+import io
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import bsrnn_oracle as O
+
+pytestmark = pytest.mark.gpu
+torch.set_grad_enabled(False)
+STAGE_TOL = 2e-4
+GATE = 1e-3
+XS = 2052
+
+
+@pytest.fixture(scope="module")
+def dev():
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return torch.device("cuda:0")
+
+
+@pytest.fixture(scope="module")
+def model(dev, oracle_sd):
+    from speechseparation_b200 import BSRNN
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = BSRNN()
+    m.load_state_dict(oracle_sd, strict=True)
+    return m.to(dev).eval()
+
+
+def rel(a, b):
+    a = a.detach().double().cpu().reshape(-1)
+    b = b.detach().double().cpu().reshape(-1)
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def to_frames(x):            # [C,2050,T] -> [C*T, XS] padded (pad filled with NaN-free junk)
+    C, F, T = x.shape
+    xf = torch.full((C * T, XS), 7.0, dtype=torch.float32, device=x.device)
+    xf[:, :F] = x.permute(0, 2, 1).reshape(C * T, F)
+    return xf
+
+
+def _ws(l, C, T, dev):
+    return torch.empty(l.bsb_workspace_bytes(C, T), dtype=torch.uint8, device=dev)
+
+
+def _s():
+    return torch.cuda.current_stream().cuda_stream
+
+
+# ---------------------------------------------------------------------------------------------
+def test_stft_pack_and_istft_vs_golden(dev, golden_dir):
+    from speechseparation_b200 import stft_pack, unpack_istft
+    g = np.load(os.path.join(golden_dir, "wrap_small.npz"))
+    wav = torch.from_numpy(g["wav"]).to(dev)
+    win = torch.hann_window(2048, device=dev)
+    for w in (win, None):                       # caller's window and the built-in table
+        x = stft_pack(wav, w)
+        assert x.shape == (2, 2050, 7)
+        assert rel(x, torch.from_numpy(g["packed"])) < 2e-6
+        assert rel(unpack_istft(x, w), torch.from_numpy(g["istft"])) < 2e-6
+        # arbitrary (non-consistent) spectrogram, non-zero DC/Nyquist imaginary parts
+        assert rel(unpack_istft(torch.from_numpy(g["xr"]).to(dev), w), torch.from_numpy(g["istft_r"])) < 2e-6
+
+
+@pytest.mark.parametrize("C,L", [(1, 1025), (3, 5000), (2, 44100), (5, 1024 * 9)])
+def test_stft_istft_vs_oracle_and_roundtrip(dev, C, L):
+    from speechseparation_b200 import stft_pack, unpack_istft
+    wav, _ = O.synth_audio(C, L, seed=L)
+    x = stft_pack(wav.to(dev))
+    assert rel(x, O.stft_pack(wav)) < 2e-6
+    T = x.shape[2]
+    if T >= 2:
+        back = unpack_istft(x)
+        assert back.shape == (C, 1024 * (T - 1))
+        assert rel(back, O.unpack_istft(O.stft_pack(wav))) < 2e-6
+        assert float((back.cpu() - wav[:, :back.shape[1]]).abs().max()) < 2e-6     # perfect reconstruction
+
+
+def test_layout_transposes_are_exact(dev):
+    from speechseparation_b200 import _lib
+    l = _lib.lib()
+    C, T = 3, 37
+    x = torch.randn(C, 2050, T, device=dev)
+    xf = torch.zeros(C * T, XS, device=dev)
+    _lib.check(l.bsb_to_frames(x.data_ptr(), C, T, xf.data_ptr(), _s()))
+    assert torch.equal(xf[:, :2050].reshape(C, T, 2050).permute(0, 2, 1), x)
+    x2 = torch.zeros_like(x)
+    _lib.check(l.bsb_from_frames(xf.data_ptr(), C, T, x2.data_ptr(), _s()))
+    assert torch.equal(x2, x)
+
+
+def test_stages_vs_oracle(dev, model, oracle_sd, golden_dir):
+    """Each stage is fed the ORACLE's input for that stage, so one failure does not mask another."""
+    from speechseparation_b200 import _lib
+    l = _lib.lib()
+    g = np.load(os.path.join(golden_dir, "offline_small.npz"))
+    x = torch.from_numpy(g["x"])
+    C, _, T = x.shape
+    st = O.forward_stages(oracle_sd, x)
+    packed = model.packed_weights(dev)
+    ws = _ws(l, C, T, dev)
+    xf = to_frames(x.to(dev))
+    R = C * T
+    # band split
+    residual = torch.zeros(R, XS, device=dev)
+    feat = torch.zeros(R, 12, 64, device=dev)
+    _lib.check(l.bsb_bandsplit(xf.data_ptr(), R, packed.data_ptr(), residual.data_ptr(), feat.data_ptr(),
+                               ws.data_ptr(), ws.numel(), _s()), "bandsplit")
+    assert rel(residual[:, :2050].reshape(C, T, 2050), st["residual"]) < STAGE_TOL
+    assert rel(feat.reshape(C, T, 12, 64), st["feat"]) < STAGE_TOL
+    assert rel(feat.reshape(C, T, 12, 64), torch.from_numpy(g["feat"])) < STAGE_TOL      # reference golden
+    # rnn blocks, each from the oracle's input
+    prev = st["feat"]
+    for j in range(4):
+        fin = prev.contiguous().to(dev)
+        fout = torch.zeros_like(fin)
+        _lib.check(l.bsb_rnn_block(j, fin.data_ptr(), C, T, packed.data_ptr(), None, None, fout.data_ptr(),
+                                   ws.data_ptr(), ws.numel(), _s()), f"rnn{j}")
+        assert rel(fout, st[f"rnn{j}"]) < STAGE_TOL, j
+        assert rel(fout, torch.from_numpy(g[f"rnn{j}"])) < STAGE_TOL, j
+        prev = st[f"rnn{j}"]
+    # decoder + mask
+    yf = torch.zeros(R, XS, device=dev)
+    res_f = to_frames(st["residual"].permute(0, 2, 1).contiguous().to(dev))
+    _lib.check(l.bsb_decode_mask(st["rnn3"].contiguous().to(dev).data_ptr(), res_f.data_ptr(), xf.data_ptr(), R,
+                                 packed.data_ptr(), yf.data_ptr(), ws.data_ptr(), ws.numel(), _s()), "decode")
+    y = yf[:, :2050].reshape(C, T, 2050).permute(0, 2, 1)
+    assert rel(y, st["y"]) < STAGE_TOL
+    assert rel(y, torch.from_numpy(g["y"])) < STAGE_TOL
+
+
+def test_forward_vs_golden_and_input_not_mutated(dev, model, golden_dir):
+    g = np.load(os.path.join(golden_dir, "offline_small.npz"))
+    x = torch.from_numpy(g["x"]).to(dev)
+    keep = x.clone()
+    y = model.forward(x)
+    assert y.shape == x.shape and y.data_ptr() != x.data_ptr() and torch.equal(x, keep)
+    assert rel(y, torch.from_numpy(g["y"])) < STAGE_TOL
+    assert rel(model(x), torch.from_numpy(g["y"])) < STAGE_TOL      # via __call__ too
+
+
+def test_forward_recurrent_vs_golden(dev, model, golden_dir):
+    g = np.load(os.path.join(golden_dir, "recurrent_small.npz"))
+    s = torch.from_numpy(g["state0"]).to(dev)
+    for h in range(g["x"].shape[0]):
+        y, s2 = model.forward_recurrent(torch.from_numpy(g["x"][h]).to(dev), s)
+        assert s2.data_ptr() != s.data_ptr()
+        assert rel(y, torch.from_numpy(g["y"][h])) < STAGE_TOL
+        assert float((s2.cpu() - torch.from_numpy(g["state"][h])).abs().max()) < 1e-4
+        s = s2
+
+
+@pytest.mark.parametrize("C,T", [(1, 1), (2, 3), (5, 130), (3, 257)])
+def test_forward_ragged_shapes_vs_oracle(dev, model, oracle_sd, C, T):
+    rs = np.random.RandomState(100 * C + T)
+    x = torch.from_numpy((rs.standard_normal((C, 2050, T)) * 2.0).astype(np.float32))
+    y = model.forward(x.to(dev))
+    assert rel(y, O.forward(oracle_sd, x)) < STAGE_TOL
+
+
+def test_recurrent_equals_offline_and_rows_independent(dev, model):
+    rs = np.random.RandomState(2)
+    C, T = 3, 6
+    x = torch.from_numpy(rs.standard_normal((C, 2050, T)).astype(np.float32)).to(dev)
+    y = model.forward(x)
+    s = torch.zeros(4, 2, C * 12, 64, device=dev)
+    ys = []
+    for t in range(T):
+        yy, s = model.forward_recurrent(x[:, :, t].contiguous(), s)
+        ys.append(yy)
+    assert rel(torch.stack(ys, 2), y) < 2e-5
+    assert torch.equal(model.forward(x[1:2]), y[1:2])                 # bit-exact row independence
+    assert float(model.forward(torch.zeros_like(x)).abs().max()) == 0.0
+
+
+def test_separate_cfg1_vs_golden_gate(dev, model, golden_dir):
+    """cfg 1: [2,176400] end to end against the reference's output (decimated golden + checksums)."""
+    g = np.load(os.path.join(golden_dir, "cfg1.npz"))
+    wav, src = O.synth_audio(1, 176400, seed=1234)
+    wav = torch.cat((wav, wav), 0)
+    out = model.separate(wav.to(dev)).cpu()
+    assert list(out.shape) == list(g["shape_out"])
+    ref_dec = torch.from_numpy(g["sep_dec"])
+    scale = float(g["sep_absmax"][0])
+    assert float((out[:, ::37] - ref_dec).abs().max()) / scale < GATE
+    assert abs(float((out.double() ** 2).sum()) - float(g["sep_sumsq"][0])) / float(g["sep_sumsq"][0]) < 1e-3
+    sis = O.si_sdr(out, torch.cat((src, src), 0)[:, :out.shape[1]]).numpy()
+    assert np.abs(sis - g["si_sdr"]).max() < 0.01
+    # the three-call path (stft_pack -> forward -> unpack_istft) agrees with the fused one
+    from speechseparation_b200 import infer
+    x, x_time = infer(model, wav.to(dev))
+    assert rel(x_time, out) < 1e-5
+    assert rel(x[:, ::7, ::5], torch.from_numpy(g["y_dec"])) < STAGE_TOL
+
+
+def test_streaming_vs_golden_and_graph_replay(dev, model, golden_dir):
+    from speechseparation_b200 import StreamingSeparator
+    g = np.load(os.path.join(golden_dir, "stream_small.npz"))
+    wav = torch.from_numpy(g["wav"])
+    for use_graph in (False, True):
+        sep = StreamingSeparator(model, rows=2, use_graph=use_graph)
+        outs = [sep.step(wav[:, h * 1024:(h + 1) * 1024].to(dev)).clone() for h in range(6)]
+        assert rel(torch.cat(outs, 1), torch.from_numpy(g["out"])) < STAGE_TOL
+        assert float((sep.current_state.cpu() - torch.from_numpy(g["state"])).abs().max()) < 1e-4
+
+
+def test_grad_request_raises_not_silent(dev, oracle_sd):
+    from speechseparation_b200 import BSRNN
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = BSRNN().to(dev)
+    with torch.enable_grad():
+        x = torch.randn(1, 2050, 2, device=dev)
+        y = m.forward(x)
+        assert y.requires_grad
+        with pytest.raises(NotImplementedError):
+            y.sum().backward()
+
+
+def test_repack_after_weight_update(dev, oracle_sd):
+    from speechseparation_b200 import BSRNN
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = BSRNN().to(dev).eval()
+    x = torch.randn(1, 2050, 3, device=dev)
+    y0 = m.forward(x)
+    m.load_state_dict(oracle_sd, strict=True)
+    y1 = m.forward(x)
+    assert rel(y1, O.forward(oracle_sd, x.cpu())) < STAGE_TOL and not torch.equal(y0, y1)
+
+
+def test_kernels_really_launch(dev, model):
+    from speechseparation_b200 import _lib
+    n0 = _lib.lib().bsb_launch_count()
+    model.forward(torch.randn(1, 2050, 2, device=dev))
+    torch.cuda.synchronize()
+    assert _lib.lib().bsb_launch_count() - n0 >= 30
