@@ -139,6 +139,9 @@ int         bsb_set_stage_timing(int enabled);
 int         bsb_stage_count(void);
 const char* bsb_stage_name(int i);
 int         bsb_stage_times(float* ms, int n);
+/* 0 (default): Linear layers with >= 128 rows run on the tensor cores (split-bf16, 3 MMAs per
+ * product, ~1e-5 of fp32); 1: force the fp32 FFMA kernel everywhere (A/B numerics checks). */
+int         bsb_set_force_fp32(int on);
 /* number of kernels launched by this library since load (all streams) */
 long long   bsb_launch_count(void);
 

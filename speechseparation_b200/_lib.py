@@ -47,6 +47,7 @@ SIGNATURES = {
     "bsb_stage_name": (C.c_char_p, [ci]),
     "bsb_stage_times": (ci, [C.POINTER(C.c_float), ci]),
     "bsb_launch_count": (cll, []),
+    "bsb_set_force_fp32": (ci, [ci]),
 }
 
 

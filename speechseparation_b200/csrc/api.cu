@@ -107,6 +107,7 @@ void set_prob(LinProb& P, const void* packed, const Lin& l, const float* A, int 
               int act, const float* res = nullptr, int ldres = 0, const float* mul = nullptr, int ldmul = 0) {
   P.A = A; P.lda = lda;
   P.W = PW(packed, l.w); P.ldw = l.Kpad;
+  P.Wh = l.Kpad64 ? PW(packed, l.wh) : nullptr; P.Wl = l.Kpad64 ? PW(packed, l.wl) : nullptr; P.ldw64 = l.Kpad64;
   P.bias = PW(packed, l.b);
   P.O = O; P.ldo = ldo;
   P.res = res; P.ldres = ldres;
@@ -166,6 +167,7 @@ int bsb_pack_weights(const void* const* src, int n_src, void* packed, void* stre
   auto F = [&](int i) { return reinterpret_cast<const float*>(src[i]); };
   auto lin = [&](const Lin& l, int iw) -> int {   // iw: index of .weight, bias follows
     CK(launch_pack_matrix(F(iw), l.N, l.K, dst + l.w, l.Kpad, s));
+    CK(launch_pack_split(F(iw), l.N, l.K, dst + l.wh, dst + l.wl, l.Kpad64, s));
     CK(launch_pack_bias(F(iw + 1), nullptr, l.N, dst + l.b, s));
     return 0;
   };
@@ -192,6 +194,8 @@ int bsb_pack_weights(const void* const* src, int n_src, void* packed, void* stre
       for (int d = 0; d < R.ndir; ++d) {
         // weight_ih, weight_hh, bias_ih, bias_hh
         CK(launch_pack_matrix(F(k), kGates, ih.K, dst + ih.w + (long long)d * kGates * ih.Kpad, ih.Kpad, s));
+        CK(launch_pack_split(F(k), kGates, ih.K, dst + ih.wh + (long long)d * kGates * ih.Kpad64 / 2,
+                             dst + ih.wl + (long long)d * kGates * ih.Kpad64 / 2, ih.Kpad64, s));
         CK(launch_pack_matrix(F(k + 1), kGates, kFeat, dst + R.hh[layer] + (long long)d * kGates * kFeat, kFeat, s));
         CK(launch_pack_bias(F(k + 2), F(k + 3), kGates, dst + ih.b + d * kGates, s));
         k += 4;
@@ -233,6 +237,7 @@ int bsb_stage_times(float* ms, int n) {
   return cnt;
 }
 long long bsb_launch_count(void) { return g_launches; }
+int bsb_set_force_fp32(int on) { set_force_ffma(on); return 0; }
 
 }  // extern "C"
 

@@ -19,11 +19,13 @@ enum Act : int { ACT_NONE = 0, ACT_LRELU = 1 };
 struct LinProb {
   const float* A;      // [M][lda], K valid columns
   const float* W;      // [Npad][ldw] zero padded (ldw = Kpad)
+  const void* Wh;      // bf16 split planes [Npad][ldw64] (tensor-core path), hi and lo
+  const void* Wl;
   const float* bias;   // [Npad]
   float* O;            // [M][ldo]
   const float* res;    // optional: v += res[m][n]   (after activation)
   const float* mul;    // optional: v *= mul[m][n]   (after res)
-  int lda, ldw, ldo, ldres, ldmul;
+  int lda, ldw, ldw64, ldo, ldres, ldmul;
   int M, N, K;
   int act;
   int tile_start;      // first tile index of this problem in the launch
@@ -36,8 +38,15 @@ struct GroupedArgs {
   int total_tiles;
 };
 
-// fills tile_start/tiles_n/total_tiles and launches (no-op when there is no work)
+// fills tile_start/tiles_n/total_tiles and launches (no-op when there is no work).
+// Dispatch by shape: M >= kTcMinRows -> tensor-core kernel (tc_linear.cu), else the FFMA kernel
+// (streaming hops, M = rows of one frame); K == 0 problems (band 11 constant) always FFMA.
+constexpr int kTcMinRows = 128;
 cudaError_t launch_grouped_linear(GroupedArgs& args, cudaStream_t s);
+cudaError_t launch_ffma_grouped_linear(GroupedArgs& args, cudaStream_t s);
+cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s);
+// 0 = shape-based dispatch (default), 1 = force the fp32 FFMA kernel everywhere (A/B checks)
+void set_force_ffma(int on);
 
 // ------------------------------------------------------------------------------------
 // LSTM recurrence over precomputed gate pre-activations.
@@ -84,6 +93,8 @@ const float2* twiddle_tables(cudaStream_t s, cudaError_t* err);  // device: [102
 // weight packing helpers
 // ------------------------------------------------------------------------------------
 cudaError_t launch_pack_matrix(const float* src, int N, int K, float* dst, int ldd, cudaStream_t s);
+// W -> bf16 hi/lo planes [N][ldd] (ldd in bf16 elements)
+cudaError_t launch_pack_split(const float* src, int N, int K, void* dst_hi, void* dst_lo, int ldd, cudaStream_t s);
 cudaError_t launch_pack_bias(const float* b1, const float* b2, int N, float* dst, cudaStream_t s);
 
 }  // namespace bsb

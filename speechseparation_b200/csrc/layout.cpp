@@ -18,8 +18,11 @@ struct Builder {
     l.K = K;
     l.Npad = rup(N, 64);
     l.Kpad = rup(K, 32);
+    l.Kpad64 = rup(K, 64);
     l.w = take((long long)l.Npad * l.Kpad);
     l.b = take(l.Npad);
+    l.wh = take((long long)l.Npad * l.Kpad64 / 2);   // bf16 plane = half as many floats
+    l.wl = take((long long)l.Npad * l.Kpad64 / 2);
     return l;
   }
 };

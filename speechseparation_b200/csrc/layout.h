@@ -3,7 +3,8 @@
 // The reference keeps 288 separate parameter tensors (bsrnn.py:328-376); the kernels read
 // one device buffer in which every Linear is stored [Npad][Kpad] row-major (the nn.Linear
 // orientation: output-major, K contiguous), zero padded to Kpad = roundup(K,32),
-// Npad = roundup(N,64), followed by its bias [Npad].  LSTM input weights of the two
+// Npad = roundup(N,64), followed by its bias [Npad].  Every Linear is stored a second time as two
+// bf16 planes (hi = bf16(W), lo = bf16(W - hi)), K padded to 64, for the tensor-core kernel.  LSTM input weights of the two
 // directions are stacked along N (fwd gates 0..255, reverse 256..511) and b_ih+b_hh are
 // summed at pack time; W_hh is kept raw [256][64] per direction.
 #pragma once
@@ -34,9 +35,10 @@ inline constexpr int hid_off(int i) { int o = 0; for (int b = 0; b < i; ++b) o +
 constexpr int kHidStride = hid_off(kRealBands);   // 2756
 
 struct Lin {            // one packed Linear
-  long long w;          // float offset of W[Npad][Kpad]
+  long long w;          // float offset of W[Npad][Kpad] (fp32)
   long long b;          // float offset of bias[Npad]
-  int N, K, Npad, Kpad;
+  long long wh, wl;     // float offsets of the bf16 split planes W ~= hi + lo, each [Npad][Kpad64] bf16
+  int N, K, Npad, Kpad, Kpad64;
 };
 
 struct RnnBlock {

@@ -166,7 +166,7 @@ grouped_linear_kernel(const __grid_constant__ GroupedArgs args) {
 
 }  // namespace
 
-cudaError_t launch_grouped_linear(GroupedArgs& args, cudaStream_t s) {
+cudaError_t launch_ffma_grouped_linear(GroupedArgs& args, cudaStream_t s) {
   int total = 0;
   for (int i = 0; i < args.nprob; ++i) {
     LinProb& P = args.p[i];
@@ -180,6 +180,22 @@ cudaError_t launch_grouped_linear(GroupedArgs& args, cudaStream_t s) {
   grouped_linear_kernel<<<total, NT, 0, s>>>(args);
   count_launch();
   return cudaGetLastError();
+}
+
+static int g_force_ffma = 0;
+void set_force_ffma(int on) { g_force_ffma = on; }
+
+cudaError_t launch_grouped_linear(GroupedArgs& args, cudaStream_t s) {
+  bool tc = !g_force_ffma && args.nprob > 0;
+  for (int i = 0; i < args.nprob; ++i)
+    if (args.p[i].K > 0 && (args.p[i].M < kTcMinRows || args.p[i].Wh == nullptr)) tc = false;
+  if (!tc) return launch_ffma_grouped_linear(args, s);
+  cudaError_t e = launch_tc_grouped_linear(args, s);
+  if (e != cudaSuccess) return e;
+  GroupedArgs rest{};                       // K == 0 problems: out = bias broadcast
+  for (int i = 0; i < args.nprob; ++i)
+    if (args.p[i].K == 0) rest.p[rest.nprob++] = args.p[i];
+  return rest.nprob ? launch_ffma_grouped_linear(rest, s) : cudaSuccess;
 }
 
 }  // namespace bsb

@@ -1,0 +1,358 @@
+// Grouped Linear layers on the 5th-gen tensor cores (tcgen05 + TMEM), split-bf16 arithmetic.
+//
+//   O[m][n] = epi( sum_k A[m][k] * W[n][k] + bias[n] ),  A, O fp32 in HBM.
+//
+// Precision: the gate is 1e-3 against the fp32 reference, which plain TF32/bf16 misses
+// (measured by emulation: TF32 1.7e-3). Each fp32 operand is split into two bf16 terms
+// (x = hi + lo, 16 mantissa bits) and the product is formed from three MMAs
+//   A_hi.W_hi + A_hi.W_lo + A_lo.W_hi      (fp32 accumulation in TMEM)
+// which reproduces the fp32 path to ~1e-5 end to end at 3 bf16 MMAs per product.
+//
+// Persistent, warp-specialised CTA (one per SM), tiles of 128 rows x up to 256 columns:
+//   warps 0-3  A producers : fp32 global -> registers -> (hi, lo) bf16 -> 128B-swizzled smem
+//   warps 4-7  W producers : pre-split bf16 weight planes (L2 resident) -> swizzled smem
+//   warp  8    MMA issuer  : one thread issues tcgen05.mma (M=128, N<=256, K=16) x 12 per 64-wide
+//                            K chunk; tcgen05.commit frees the smem stage / publishes the tile
+//   warps 9-12 epilogue    : tcgen05.ld TMEM -> registers, bias + LeakyReLU (+residual, *x), store
+// Two smem stages (mbarrier full/empty ring) and two 256-column TMEM accumulators (full/empty
+// barriers) let producer, tensor core and epilogue overlap across K chunks and across tiles.
+#include "kernels.cuh"
+#include "ptx.cuh"
+
+namespace bsb {
+namespace {
+
+using namespace ptx;
+
+constexpr int BM = 128;              // rows per tile (UMMA M)
+constexpr int BK = 64;               // bf16 elements per K chunk = one 128-byte swizzle row
+constexpr int BN_MAX = 256;          // columns per tile (UMMA N <= 256)
+constexpr int STAGES = 2;
+constexpr int A_PLANE = BM * 128;            // bytes of one A plane per stage (16 KB)
+constexpr int W_PLANE = BN_MAX * 128;        // bytes of one W plane per stage (32 KB)
+constexpr int STAGE_BYTES = 2 * A_PLANE + 2 * W_PLANE;   // 96 KB
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024;  // + alignment slack
+constexpr int N_A_WARPS = 4, N_W_WARPS = 4, N_EPI_WARPS = 4;
+constexpr int MMA_WARP = N_A_WARPS + N_W_WARPS;          // 8
+constexpr int EPI_WARP0 = MMA_WARP + 1;                  // 9
+constexpr int THREADS = (N_A_WARPS + N_W_WARPS + 1 + N_EPI_WARPS) * 32;   // 416
+constexpr int N_PRODUCERS = (N_A_WARPS + N_W_WARPS) * 32;                 // 256
+constexpr int TMEM_COLS = 512;       // 2 accumulators x 256 fp32 columns
+
+struct TcProb {
+  const float* A;
+  const __nv_bfloat16* Wh;   // [Npad][ldw] bf16, hi plane
+  const __nv_bfloat16* Wl;   // lo plane
+  const float* bias;
+  float* O;
+  const float* res;
+  const float* mul;
+  int lda, ldw, ldo, ldres, ldmul;
+  int M, N, K, act;
+  int tile_start, tiles_m;
+};
+struct TcArgs {
+  TcProb p[kMaxProb];
+  int nprob;
+  int total_tiles;
+};
+
+struct Tile {
+  int pi, m0, n0, bn;    // problem, first row, first column, columns in this tile (multiple of 64)
+};
+
+__device__ __forceinline__ Tile decode_tile(const TcArgs& args, int tile) {
+  int pi = 0;
+  while (pi + 1 < args.nprob && tile >= args.p[pi + 1].tile_start) ++pi;
+  const TcProb& P = args.p[pi];
+  const int local = tile - P.tile_start;
+  Tile t;
+  t.pi = pi;
+  t.m0 = (local % P.tiles_m) * BM;            // m fastest: concurrent CTAs share the W tile in L2
+  t.n0 = (local / P.tiles_m) * BN_MAX;
+  const int npad = (P.N + 63) & ~63;
+  t.bn = min(BN_MAX, npad - t.n0);
+  return t;
+}
+
+// byte offset of 16-byte chunk `c` (0..7) of row `r` inside a 128B-swizzled K-major plane
+__device__ __forceinline__ uint32_t sw128(int r, int c) { return (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4)); }
+
+// ---- A producer: 128 rows x 64 k of fp32 -> hi/lo bf16 planes --------------------------------
+__device__ __forceinline__ void produce_a(const TcProb& P, int m0, int k0, uint8_t* a_hi, uint8_t* a_lo, int t) {
+  const bool vec = ((P.lda & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.A) & 15) == 0);
+  float4 v[8][2];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int g = t + 128 * i;          // 8-float group: row g/8, chunk g%8
+    const int r = g >> 3, c = g & 7;
+    const int m = m0 + r, k = k0 + c * 8;
+    float4 x0 = make_float4(0.f, 0.f, 0.f, 0.f), x1 = x0;
+    if (m < P.M && k < P.K) {
+      const float* p = P.A + (long long)m * P.lda + k;
+      if (vec && k + 7 < P.K) {
+        x0 = __ldg(reinterpret_cast<const float4*>(p));
+        x1 = __ldg(reinterpret_cast<const float4*>(p) + 1);
+      } else {
+        float e[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) e[j] = (k + j < P.K) ? __ldg(p + j) : 0.f;
+        x0 = make_float4(e[0], e[1], e[2], e[3]);
+        x1 = make_float4(e[4], e[5], e[6], e[7]);
+      }
+    }
+    v[i][0] = x0;
+    v[i][1] = x1;
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int g = t + 128 * i;
+    const int r = g >> 3, c = g & 7;
+    uint4 h, l;
+    split2(v[i][0].x, v[i][0].y, h.x, l.x);
+    split2(v[i][0].z, v[i][0].w, h.y, l.y);
+    split2(v[i][1].x, v[i][1].y, h.z, l.z);
+    split2(v[i][1].z, v[i][1].w, h.w, l.w);
+    const uint32_t off = sw128(r, c);
+    *reinterpret_cast<uint4*>(a_hi + off) = h;
+    *reinterpret_cast<uint4*>(a_lo + off) = l;
+  }
+}
+
+// ---- W producer: bn rows x 64 k of pre-split bf16 (two planes) ------------------------------------
+__device__ __forceinline__ void produce_w(const TcProb& P, int n0, int bn, int k0, uint8_t* w_hi, uint8_t* w_lo, int t) {
+  const int groups = bn * 8;            // 16-byte chunks per plane
+  const __nv_bfloat16* gh = P.Wh + (long long)n0 * P.ldw + k0;
+  const __nv_bfloat16* gl = P.Wl + (long long)n0 * P.ldw + k0;
+#pragma unroll 4
+  for (int g = t; g < groups; g += 128) {
+    const int r = g >> 3, c = g & 7;
+    const long long src = (long long)r * P.ldw + c * 8;
+    const uint4 h = __ldg(reinterpret_cast<const uint4*>(gh + src));
+    const uint4 l = __ldg(reinterpret_cast<const uint4*>(gl + src));
+    const uint32_t off = sw128(r, c);
+    *reinterpret_cast<uint4*>(w_hi + off) = h;
+    *reinterpret_cast<uint4*>(w_lo + off) = l;
+  }
+}
+
+__device__ __forceinline__ float lrelu(float v) { return v > 0.f ? v : v * 0.01f; }
+
+__global__ void __launch_bounds__(THREADS, 1)
+tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bar_full[STAGES], bar_empty[STAGES], bar_tfull[2], bar_tempty[2];
+  __shared__ uint32_t tmem_slot;
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  // 1024-byte aligned operand area (SWIZZLE_128B atoms)
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(smem_u32(&bar_full[s]), N_PRODUCERS);
+      mbar_init(smem_u32(&bar_empty[s]), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(smem_u32(&bar_tfull[a]), 1);
+      mbar_init(smem_u32(&bar_tempty[a]), N_EPI_WARPS * 32);
+    }
+    fence_mbar_init();
+  }
+  if (warp == MMA_WARP) {
+    tmem_alloc(smem_u32(&tmem_slot), TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  if (warp < MMA_WARP) {
+    // ================= producers =================
+    const bool is_a = warp < N_A_WARPS;
+    const int t = is_a ? tid : tid - N_A_WARPS * 32;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
+      const Tile T = decode_tile(args, tile);
+      const TcProb& P = args.p[T.pi];
+      const int nk = (P.K + BK - 1) / BK;
+      for (int kc = 0; kc < nk; ++kc) {
+        mbar_wait(smem_u32(&bar_empty[stage]), phase ^ 1);
+        uint8_t* sb = smem_gen + stage * STAGE_BYTES;
+        if (is_a) produce_a(P, T.m0, kc * BK, sb, sb + A_PLANE, t);
+        else produce_w(P, T.n0, T.bn, kc * BK, sb + 2 * A_PLANE, sb + 2 * A_PLANE + W_PLANE, t);
+        fence_proxy_async_smem();
+        mbar_arrive(smem_u32(&bar_full[stage]));
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == MMA_WARP) {
+    // ================= MMA issuer =================
+    int stage = 0, acc = 0;
+    uint32_t phase = 0, acc_phase = 0;
+    for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
+      const Tile T = decode_tile(args, tile);
+      const TcProb& P = args.p[T.pi];
+      const int nk = (P.K + BK - 1) / BK;
+      mbar_wait(smem_u32(&bar_tempty[acc]), acc_phase ^ 1);   // epilogue has drained this accumulator
+      tc_fence_after();
+      const uint32_t idesc = make_idesc_bf16(BM, T.bn);
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN_MAX);
+      for (int kc = 0; kc < nk; ++kc) {
+        mbar_wait(smem_u32(&bar_full[stage]), phase);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t sb = smem_base + stage * STAGE_BYTES;
+          const uint64_t a_hi = make_sw128_desc(sb);
+          const uint64_t a_lo = make_sw128_desc(sb + A_PLANE);
+          const uint64_t w_hi = make_sw128_desc(sb + 2 * A_PLANE);
+          const uint64_t w_lo = make_sw128_desc(sb + 2 * A_PLANE + W_PLANE);
+#pragma unroll
+          for (int kk = 0; kk < BK / 16; ++kk) {
+            const uint64_t adv = (uint64_t)(kk * 32 >> 4);    // 16 bf16 = 32 bytes along K
+            mma_bf16_ss(d_tmem, a_lo + adv, w_hi + adv, idesc, (kc | kk) != 0);   // small terms first
+            mma_bf16_ss(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
+            mma_bf16_ss(d_tmem, a_hi + adv, w_hi + adv, idesc, 1);
+          }
+          mma_commit(smem_u32(&bar_empty[stage]));             // smem stage reusable once these MMAs retire
+          if (kc == nk - 1) mma_commit(smem_u32(&bar_tfull[acc]));
+        }
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  } else {
+    // ================= epilogue =================
+    const int q = warp & 3;                 // TMEM lane quarter this warp may access
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
+      const Tile T = decode_tile(args, tile);
+      const TcProb& P = args.p[T.pi];
+      mbar_wait(smem_u32(&bar_tfull[acc]), acc_phase);
+      tc_fence_after();
+      const int m = T.m0 + q * 32 + lane;
+      const bool row_ok = m < P.M;
+      float* orow = P.O + (long long)m * P.ldo;
+      const float* rrow = P.res ? P.res + (long long)m * P.ldres : nullptr;
+      const float* mrow = P.mul ? P.mul + (long long)m * P.ldmul : nullptr;
+      const bool o_vec = ((P.ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.O) & 15) == 0);
+      const bool r_vec = rrow && ((P.ldres & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.res) & 15) == 0);
+      const bool m_vec = mrow && ((P.ldmul & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.mul) & 15) == 0);
+      const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN_MAX);
+      for (int cc = 0; cc < T.bn / 32; ++cc) {
+        uint32_t r[32];
+        tmem_ld_32x32(tbase + cc * 32, r);
+        tmem_ld_wait();
+        const int nb = T.n0 + cc * 32;
+        if (row_ok && nb < P.N) {
+#pragma unroll
+          for (int j4 = 0; j4 < 8; ++j4) {
+            const int n = nb + j4 * 4;
+            if (n >= P.N) break;
+            const float4 bb = __ldg(reinterpret_cast<const float4*>(P.bias + n));   // bias padded to Npad
+            float v[4] = {__uint_as_float(r[j4 * 4 + 0]) + bb.x, __uint_as_float(r[j4 * 4 + 1]) + bb.y,
+                          __uint_as_float(r[j4 * 4 + 2]) + bb.z, __uint_as_float(r[j4 * 4 + 3]) + bb.w};
+            if (P.act == ACT_LRELU) {
+#pragma unroll
+              for (int e = 0; e < 4; ++e) v[e] = lrelu(v[e]);
+            }
+            const bool full4 = n + 3 < P.N;
+            if (rrow) {
+              if (r_vec && full4) {
+                const float4 x = __ldg(reinterpret_cast<const float4*>(rrow + n));
+                v[0] += x.x; v[1] += x.y; v[2] += x.z; v[3] += x.w;
+              } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) if (n + e < P.N) v[e] += __ldg(rrow + n + e);
+              }
+            }
+            if (mrow) {
+              if (m_vec && full4) {
+                const float4 x = __ldg(reinterpret_cast<const float4*>(mrow + n));
+                v[0] *= x.x; v[1] *= x.y; v[2] *= x.z; v[3] *= x.w;
+              } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) if (n + e < P.N) v[e] *= __ldg(mrow + n + e);
+              }
+            }
+            if (o_vec && full4) {
+              *reinterpret_cast<float4*>(orow + n) = make_float4(v[0], v[1], v[2], v[3]);
+            } else {
+#pragma unroll
+              for (int e = 0; e < 4; ++e) if (n + e < P.N) orow[n + e] = v[e];
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(smem_u32(&bar_tempty[acc]));
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == MMA_WARP) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+int g_sm_count[64] = {};
+
+}  // namespace
+
+// Launch the problems of `args` that have K > 0 on the tensor-core kernel. Problems are taken
+// in descending-K order so that the static round-robin schedule ends with the cheap tiles.
+cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(tc_grouped_linear_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev >= 0 && dev < 64 && g_sm_count[dev] == 0) {
+    e = cudaDeviceGetAttribute(&g_sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) return e;
+  }
+  const int sms = (dev >= 0 && dev < 64) ? g_sm_count[dev] : 148;
+
+  int order[kMaxProb], n = 0;
+  for (int i = 0; i < args.nprob; ++i)
+    if (args.p[i].K > 0 && args.p[i].M > 0 && args.p[i].N > 0) order[n++] = i;
+  for (int i = 1; i < n; ++i)               // insertion sort by K descending
+    for (int j = i; j > 0 && args.p[order[j]].K > args.p[order[j - 1]].K; --j) {
+      const int t = order[j]; order[j] = order[j - 1]; order[j - 1] = t;
+    }
+  TcArgs ta{};
+  int total = 0;
+  for (int i = 0; i < n; ++i) {
+    const LinProb& L = args.p[order[i]];
+    TcProb& P = ta.p[i];
+    P.A = L.A; P.Wh = reinterpret_cast<const __nv_bfloat16*>(L.Wh); P.Wl = reinterpret_cast<const __nv_bfloat16*>(L.Wl);
+    P.bias = L.bias; P.O = L.O; P.res = L.res; P.mul = L.mul;
+    P.lda = L.lda; P.ldw = L.ldw64; P.ldo = L.ldo; P.ldres = L.ldres; P.ldmul = L.ldmul;
+    P.M = L.M; P.N = L.N; P.K = L.K; P.act = L.act;
+    P.tile_start = total;
+    P.tiles_m = (L.M + BM - 1) / BM;
+    total += P.tiles_m * ((L.N + BN_MAX - 1) / BN_MAX);
+  }
+  ta.nprob = n;
+  ta.total_tiles = total;
+  if (total == 0) return cudaSuccess;
+  const int grid = total < sms ? total : sms;
+  tc_grouped_linear_kernel<<<grid, THREADS, SMEM_BYTES, s>>>(ta);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace bsb

@@ -241,3 +241,41 @@ def test_kernels_really_launch(dev, model):
     model.forward(torch.randn(1, 2050, 2, device=dev))
     torch.cuda.synchronize()
     assert _lib.lib().bsb_launch_count() - n0 >= 30
+
+
+def test_tensor_core_linears_match_fp32_kernels(dev, model, oracle_sd):
+    """Rows >= 128 route every Linear through the tcgen05 split-bf16 kernel; compare it with the
+    fp32 FFMA kernel (forced) and with the oracle, stage by stage, on ragged row counts."""
+    from speechseparation_b200 import _lib
+    l = _lib.lib()
+    packed = model.packed_weights(dev)
+    for C, T in [(1, 128), (3, 131), (2, 300)]:
+        rs = np.random.RandomState(C * 1000 + T)
+        x = torch.from_numpy((rs.standard_normal((C, 2050, T)) * 2.0).astype(np.float32))
+        R = C * T
+        ws = _ws(l, C, T, dev)
+        xf = to_frames(x.to(dev))
+        outs = {}
+        for force in (1, 0):
+            l.bsb_set_force_fp32(force)
+            residual = torch.zeros(R, XS, device=dev)
+            feat = torch.zeros(R, 12, 64, device=dev)
+            _lib.check(l.bsb_bandsplit(xf.data_ptr(), R, packed.data_ptr(), residual.data_ptr(), feat.data_ptr(),
+                                       ws.data_ptr(), ws.numel(), _s()), "bandsplit")
+            f1 = torch.zeros_like(feat)
+            _lib.check(l.bsb_rnn_block(0, feat.data_ptr(), C, T, packed.data_ptr(), None, None, f1.data_ptr(),
+                                       ws.data_ptr(), ws.numel(), _s()), "rnn0")
+            yf = torch.zeros(R, XS, device=dev)
+            _lib.check(l.bsb_decode_mask(f1.data_ptr(), residual.data_ptr(), xf.data_ptr(), R, packed.data_ptr(),
+                                         yf.data_ptr(), ws.data_ptr(), ws.numel(), _s()), "decode")
+            torch.cuda.synchronize()
+            outs[force] = (residual[:, :2050].clone(), feat.clone(), f1.clone(), yf[:, :2050].clone())
+        l.bsb_set_force_fp32(0)
+        for name, a, b in zip(("residual", "feat", "rnn0", "y"), outs[0], outs[1]):
+            for i, off in enumerate(O.BAND_OFFS[:11]) if name in ("residual", "y") else []:
+                d = O.BAND_DIMS[i]
+                assert rel(a[:, off:off + d], b[:, off:off + d]) < 1e-4, (name, "band", i, C, T)
+            assert rel(a, b) < 5e-5, (name, C, T)
+        st = O.forward_stages(oracle_sd, x)
+        assert rel(outs[0][0].reshape(C, T, 2050), st["residual"]) < 5e-5
+        assert rel(outs[0][1].reshape(C, T, 12, 64), st["feat"]) < 5e-5
