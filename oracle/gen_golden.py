@@ -31,9 +31,12 @@ OUT = os.path.join(ROOT, "tests", "golden")
 
 
 def load_reference():
-    sys.path.insert(0, REF)
+    # by file path under a private name: the repo root ships its own `bsrnn` drop-in shim
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("reference_bsrnn", os.path.join(REF, "bsrnn.py"))
+    ref = importlib.util.module_from_spec(spec)
     with contextlib.redirect_stdout(io.StringIO()):      # ctor prints the band table, bsrnn.py:351
-        import bsrnn as ref
+        spec.loader.exec_module(ref)
     return ref
 
 

@@ -123,9 +123,12 @@ def test_invariants_recurrent_equals_offline_and_row_independence(oracle_sd):
 
 @pytest.mark.skipif(not os.path.exists("/root/reference/bsrnn.py"), reason="reference not on this box")
 def test_oracle_vs_imported_reference(oracle_sd):
-    sys.path.insert(0, "/root/reference")
+    # by file path under a private name: the repo root ships its own `bsrnn` drop-in shim
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("reference_bsrnn", "/root/reference/bsrnn.py")
+    ref = importlib.util.module_from_spec(spec)
     with contextlib.redirect_stdout(io.StringIO()):
-        import bsrnn as ref
+        spec.loader.exec_module(ref)
         m = ref.BSRNN()
     m.load_state_dict(oracle_sd, strict=True)
     m.eval()
