@@ -198,6 +198,9 @@ int bsb_pack_weights(const void* const* src, int n_src, void* packed, void* stre
                              dst + ih.wl + (long long)d * kGates * ih.Kpad64 / 2, ih.Kpad64, s));
         CK(launch_pack_matrix(F(k + 1), kGates, kFeat, dst + R.hh[layer] + (long long)d * kGates * kFeat, kFeat, s));
         CK(launch_pack_bias(F(k + 2), F(k + 3), kGates, dst + ih.b + d * kGates, s));
+        CK(launch_pack_lstm_tc(F(k), F(k + 1), F(k + 2), F(k + 3), layer == 0 ? F(I.rnn[j]) : nullptr,
+                               layer == 0 ? F(I.rnn[j] + 1) : nullptr, ih.K, dst + R.tcw[layer][d],
+                               dst + R.tcb[layer][d], s));
         k += 4;
       }
     }
@@ -293,6 +296,27 @@ int run_rnn_block(int j, const float* fin, int C, int T, const void* packed, con
   const long long rows = (long long)C * T * kBands;
   const int ldx = kGates * R.ndir, ldh = kFeat * R.ndir;
   char nm[40];
+  if (band && (long long)C * T >= kLstmTcMinSeq && !force_ffma()) {
+    // tensor-core path: fc_in and the W_ih projections are fused into the layer kernels (lstm_tc.cu)
+    float* hl[2] = {w.hbuf, w.xproj};                 // layer outputs [rows][128] (xproj is free here)
+    for (int layer = 0; layer < 2; ++layer) {
+      LstmTcArgs a{};
+      a.kin = tc_lstm_kin(layer, R.ndir);
+      a.x = layer == 0 ? fin : hl[0];
+      a.x_step = a.kin; a.x_seq = (long long)kBands * a.kin;
+      a.hout = hl[layer];
+      a.h_step = ldh; a.h_seq = (long long)kBands * ldh;
+      for (int d = 0; d < R.ndir; ++d) { a.wimg[d] = PW(packed, R.tcw[layer][d]); a.bias[d] = PW(packed, R.tcb[layer][d]); }
+      a.nseq = C * T; a.nsteps = kBands; a.ndir = R.ndir;
+      CK(launch_lstm_tc(a, s));
+      std::snprintf(nm, sizeof(nm), "rnn%d.rec%d", j, layer);
+      mark(nm, s);
+    }
+    CKI(single_linear(packed, R.fc, hl[1], ldh, fout, kFeat, rows, ACT_NONE, fin, kFeat, s));
+    std::snprintf(nm, sizeof(nm), "rnn%d.fc", j);
+    mark(nm, s);
+    return 0;
+  }
   CKI(single_linear(packed, R.fc_in, fin, kFeat, w.t64, kFeat, rows, ACT_NONE, nullptr, 0, s));
   for (int layer = 0; layer < 2; ++layer) {
     const float* in = layer == 0 ? w.t64 : w.hbuf;

@@ -68,6 +68,21 @@ struct LstmArgs {
 };
 cudaError_t launch_lstm(const LstmArgs& a, cudaStream_t s);
 
+// One LSTM layer with the input projection fused, on tcgen05 tensor cores (lstm_tc.cu): tiles of
+// 128 sequences, zero initial state. element (seq, step, k) of the input is x[seq*x_seq + step*x_step + k],
+// h(seq, step, dir*64 + u) is written to hout[seq*h_seq + step*h_step + dir*64 + u].
+struct LstmTcArgs {
+  const float* x;
+  float* hout;
+  const void* wimg[2];       // per direction: layout.h RnnBlock::tcw image
+  const float* bias[2];      // per direction: RnnBlock::tcb
+  long long x_seq, x_step, h_seq, h_step;
+  int nseq, nsteps, ndir, kin;
+};
+cudaError_t launch_lstm_tc(const LstmTcArgs& a, cudaStream_t s);
+constexpr int kLstmTcMinSeq = 128;   // below one full tile the FFMA recurrence is used
+int force_ffma();
+
 // ------------------------------------------------------------------------------------
 // signal kernels
 // ------------------------------------------------------------------------------------
@@ -96,5 +111,9 @@ cudaError_t launch_pack_matrix(const float* src, int N, int K, float* dst, int l
 // W -> bf16 hi/lo planes [N][ldd] (ldd in bf16 elements)
 cudaError_t launch_pack_split(const float* src, int N, int K, void* dst_hi, void* dst_lo, int ldd, cudaStream_t s);
 cudaError_t launch_pack_bias(const float* b1, const float* b2, int N, float* dst, cudaStream_t s);
+// tensor-core LSTM layer image + bias (layout.h RnnBlock::tcw/tcb); w_in/b_in = fc_in to fold (layer 0) or null
+cudaError_t launch_pack_lstm_tc(const float* w_ih, const float* w_hh, const float* b_ih, const float* b_hh,
+                                const float* w_in, const float* b_in, int kin, void* img, float* bias,
+                                cudaStream_t s);
 
 }  // namespace bsb

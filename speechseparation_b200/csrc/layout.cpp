@@ -52,6 +52,11 @@ Layout build_layout() {
       R.hh[layer] = B.take((long long)R.ndir * kGates * kFeat);
     }
     R.fc = B.lin(kFeat, kFeat * R.ndir);
+    for (int layer = 0; layer < 2; ++layer)
+      for (int d = 0; d < R.ndir; ++d) {
+        R.tcw[layer][d] = B.take(tc_lstm_img_floats(layer, R.ndir));
+        R.tcb[layer][d] = B.take(kGates);
+      }
   }
   for (int i = 0; i < kRealBands; ++i) {       // bandFCs_back, bsrnn.py:361-369
     int d = kBandD[i], h = imax(d, kMaskHidden);

@@ -47,7 +47,20 @@ struct RnnBlock {
   long long hh[2];      // per layer: float offset of W_hh [ndir][256][64]
   Lin fc;               // 64*ndir -> 64
   int ndir;
+  // tensor-core LSTM layer images (lstm_tc.cu), per [layer][dir]:
+  //   tcw: bf16 hi/lo planes of the concatenated [W_ih' | W_hh] matrix, rows permuted to
+  //        n = 4*unit + gate and pre-scaled by -log2(e) (i,f,o) / -2*log2(e) (g), stored as the
+  //        128B-swizzled shared-memory image [plane][k-chunk of 64][256 rows][64] the kernel copies
+  //        verbatim. Layer 0 has fc_in folded in: W_ih' = W_ih.W_in, b' = b + W_ih.b_in.
+  //   tcb: fp32 [256] bias in the same row order and scaling.
+  long long tcw[2][2];
+  long long tcb[2][2];
 };
+inline constexpr int tc_lstm_kin(int layer, int ndir) { return layer == 0 ? kFeat : kFeat * ndir; }
+inline constexpr int tc_lstm_chunks(int layer, int ndir) { return (tc_lstm_kin(layer, ndir) + kFeat) / 64; }
+inline constexpr long long tc_lstm_img_floats(int layer, int ndir) {   // 2 planes x chunks x 256 x 64 bf16
+  return (long long)tc_lstm_chunks(layer, ndir) * kGates * 64;
+}
 
 struct Layout {
   Lin pre[kRealBands][2];

@@ -184,6 +184,7 @@ cudaError_t launch_ffma_grouped_linear(GroupedArgs& args, cudaStream_t s) {
 
 static int g_force_ffma = 0;
 void set_force_ffma(int on) { g_force_ffma = on; }
+int force_ffma() { return g_force_ffma; }
 
 cudaError_t launch_grouped_linear(GroupedArgs& args, cudaStream_t s) {
   bool tc = !g_force_ffma && args.nprob > 0;

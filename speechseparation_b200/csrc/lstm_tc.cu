@@ -1,0 +1,243 @@
+// One LSTM layer (nn.LSTM semantics, bsrnn.py:70) of one direction on the 5th-gen tensor cores,
+// input projection fused: for a tile of 128 sequences a CTA computes, step after step,
+//
+//   gates[128 x 256] = [x_t | h_{t-1}] . [W_ih' | W_hh]^T         (tcgen05.mma, fp32 in TMEM)
+//   c_t = sig(f).c_{t-1} + sig(i).tanh(g),  h_t = sig(o).tanh(c_t)   (epilogue warps)
+//
+// so neither the gate pre-activations (2 KB per sequence-step) nor fc_in's output ever reach HBM
+// (fc_in, bsrnn.py:80, is folded into W_ih' at pack time, layout.h). One CTA per SM:
+//
+//   shared memory : the whole [256 x (KIN+64)] weight matrix as bf16 hi/lo planes, 128B-swizzled
+//                   K-major (128 KB for KIN=64, 192 KB for KIN=128), loaded once per CTA
+//   tensor memory : cols [0,256) gate accumulators; [256,320) h_{t-1} as bf16 hi|lo (A operand);
+//                   [320,320+KIN) x_t as bf16 hi|lo (A operand). A operands never touch smem:
+//                   the thread that owns sequence row r writes them with tcgen05.st (lane = row).
+//   warps 0-7     : epilogue; warp w owns TMEM lanes 32(w%4).. and hidden units 32(w/4)..+31 of them
+//   warp  8       : one thread issues the MMAs: 3 bf16 products per fp32 product (x = hi + lo,
+//                   hi.hi + hi.lo + lo.hi), M=128, N=256, K=16
+//
+// Gate rows are permuted to n = 4*unit + gate so a thread reads the four gates of a unit from
+// four adjacent TMEM columns, and pre-scaled by -log2(e) (i,f,o) / -2.log2(e) (g) so the
+// accumulator is directly the ex2 argument. The cell update shares reciprocals
+// (c' = [c.(1+ei)(1+eg) + (1-eg)(1+ef)] / [(1+ef)(1+ei)(1+eg)]): 5 ex2 + 2 rcp per cell.
+#include "kernels.cuh"
+#include "ptx.cuh"
+
+namespace bsb {
+namespace {
+
+using namespace ptx;
+
+constexpr int TILE = 128;
+constexpr int N_EPI_WARPS = 8;
+constexpr int THREADS = (N_EPI_WARPS + 1) * 32;
+constexpr int COL_ACC = 0, COL_AH = 256, COL_AX = 320;
+constexpr int CHUNK_BYTES = kGates * 128;          // one 64-wide K chunk of one plane: 32 KB
+constexpr float kClamp = 40.f;                     // ex2 argument cap: (1+2^40)^3 stays finite
+
+template <int KIN>
+struct Cfg {
+  static constexpr int NCH = (KIN + kFeat) / 64;            // K chunks: x part then the h part
+  static constexpr int PLANE = NCH * CHUNK_BYTES;
+  static constexpr int W_BYTES = 2 * PLANE;
+  static constexpr int SMEM = W_BYTES + kGates * 4 + 1024;  // + bias + alignment slack
+  static constexpr int XH = KIN / 2;                        // x floats per epilogue thread
+};
+
+template <int KIN>
+__global__ void __launch_bounds__(THREADS, 1)
+lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
+  using C = Cfg<KIN>;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bar_ready, bar_full;
+  __shared__ uint32_t tmem_slot;
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int dir = blockIdx.y;
+  const bool reverse = dir == 1;
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  float* bias_s = reinterpret_cast<float*>(smem_gen + C::W_BYTES);
+
+  if (tid == 0) {
+    mbar_init(smem_u32(&bar_ready), N_EPI_WARPS * 32);
+    mbar_init(smem_u32(&bar_full), 1);
+    fence_mbar_init();
+  }
+  if (warp == N_EPI_WARPS) {
+    tmem_alloc(smem_u32(&tmem_slot), 512);
+    tmem_relinquish();
+  }
+  // weights: the packed image is already the swizzled shared-memory layout
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(a.wimg[dir]);
+    uint4* dst = reinterpret_cast<uint4*>(smem_gen);
+    for (int i = tid; i < C::W_BYTES / 16; i += THREADS) dst[i] = __ldg(src + i);
+    for (int i = tid; i < kGates; i += THREADS) bias_s[i] = __ldg(a.bias[dir] + i);
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  if (warp < N_EPI_WARPS) {
+    // ================= epilogue / operand producer =================
+    const int q = warp & 3, hf = warp >> 2;
+    const int row = q * 32 + lane;
+    const long long seq = (long long)blockIdx.x * TILE + row;
+    const bool valid = seq < a.nseq;
+    const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16);
+    const float* xrow = a.x + seq * a.x_seq + hf * C::XH;
+    float* hrow = a.hout + seq * a.h_seq + dir * kFeat + hf * 32;
+
+    float xr[C::XH];
+    auto load_x = [&](int step) {
+      if (valid) {
+        const float4* p = reinterpret_cast<const float4*>(xrow + (long long)step * a.x_step);
+#pragma unroll
+        for (int i = 0; i < C::XH / 4; ++i) {
+          const float4 v = __ldg(p + i);
+          xr[4 * i + 0] = v.x; xr[4 * i + 1] = v.y; xr[4 * i + 2] = v.z; xr[4 * i + 3] = v.w;
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < C::XH; ++i) xr[i] = 0.f;
+      }
+    };
+    auto store_x = [&]() {     // bf16 hi/lo pairs -> TMEM A operand columns of this thread's k range
+#pragma unroll
+      for (int blk = 0; blk < C::XH / 32; ++blk) {
+        uint32_t hi[16], lo[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) split2(xr[blk * 32 + 2 * i], xr[blk * 32 + 2 * i + 1], hi[i], lo[i]);
+        const uint32_t col = COL_AX + hf * (KIN / 4) + blk * 16;
+        tmem_st_32x16(tlane + col, hi);
+        tmem_st_32x16(tlane + col + KIN / 2, lo);
+      }
+    };
+
+    float c[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) c[i] = 0.f;
+
+    load_x(reverse ? a.nsteps - 1 : 0);
+    store_x();
+    tmem_st_wait();
+    tc_fence_before();
+    mbar_arrive(smem_u32(&bar_ready));
+
+    for (int it = 0; it < a.nsteps; ++it) {
+      const int step = reverse ? a.nsteps - 1 - it : it;
+      const bool more = it + 1 < a.nsteps;
+      if (more) load_x(reverse ? step - 1 : step + 1);       // in flight while the MMAs run
+      mbar_wait(smem_u32(&bar_full), it & 1);
+      tc_fence_after();
+      float* hdst = hrow + (long long)step * a.h_step;
+#pragma unroll
+      for (int ch = 0; ch < 4; ++ch) {                       // 8 units = 32 accumulator columns
+        uint32_t r[32];
+        tmem_ld_32x32(tlane + COL_ACC + hf * 128 + ch * 32, r);
+        tmem_ld_wait();
+        float h[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 b = *reinterpret_cast<const float4*>(bias_s + hf * 128 + ch * 32 + j * 4);
+          const float ti = fminf(__uint_as_float(r[4 * j + 0]) + b.x, kClamp);
+          const float tf = fminf(__uint_as_float(r[4 * j + 1]) + b.y, kClamp);
+          const float tg = fminf(__uint_as_float(r[4 * j + 2]) + b.z, kClamp);
+          const float to = fminf(__uint_as_float(r[4 * j + 3]) + b.w, kClamp);
+          const float ei = ex2_approx(ti), ef = ex2_approx(tf), eg = ex2_approx(tg), eo = ex2_approx(to);
+          const float pi = 1.f + ei, pf = 1.f + ef, pg = 1.f + eg;
+          const float pig = pi * pg;
+          const float num = fmaf(c[ch * 8 + j], pig, (1.f - eg) * pf);
+          const float cn = num * rcp_approx(pf * pig);
+          c[ch * 8 + j] = cn;
+          const float ec = ex2_approx(fminf(cn * -2.885390081777927f, kClamp));
+          h[j] = (1.f - ec) * rcp_approx((1.f + eo) * (1.f + ec));
+        }
+        if (valid) {
+          *reinterpret_cast<float4*>(hdst + ch * 8) = make_float4(h[0], h[1], h[2], h[3]);
+          *reinterpret_cast<float4*>(hdst + ch * 8 + 4) = make_float4(h[4], h[5], h[6], h[7]);
+        }
+        if (more) {
+          uint32_t hi[4], lo[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) split2(h[2 * i], h[2 * i + 1], hi[i], lo[i]);
+          const uint32_t col = COL_AH + hf * 16 + ch * 4;
+          tmem_st_32x4(tlane + col, hi);
+          tmem_st_32x4(tlane + col + 32, lo);
+        }
+      }
+      if (more) {
+        store_x();
+        tmem_st_wait();
+        tc_fence_before();
+        mbar_arrive(smem_u32(&bar_ready));
+      }
+    }
+  } else {
+    // ================= MMA issuer =================
+    const uint32_t idesc = make_idesc_bf16(TILE, kGates);
+    const uint32_t d_tmem = tmem_base + COL_ACC;
+    for (int it = 0; it < a.nsteps; ++it) {
+      mbar_wait(smem_u32(&bar_ready), it & 1);
+      tc_fence_after();
+      if (lane == 0) {
+        uint32_t accumulate = 0;
+        const int nch = it == 0 ? C::NCH - 1 : C::NCH;       // h_{-1} = 0: skip the W_hh chunk
+        for (int ch = 0; ch < nch; ++ch) {
+          const bool hpart = ch == C::NCH - 1;
+          const uint32_t a_hi0 = tmem_base + (hpart ? COL_AH : COL_AX + ch * 32);
+          const uint32_t a_lo0 = a_hi0 + (hpart ? 32 : KIN / 2);
+          const uint64_t w_hi = make_sw128_desc(smem_base + ch * CHUNK_BYTES);
+          const uint64_t w_lo = make_sw128_desc(smem_base + C::PLANE + ch * CHUNK_BYTES);
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk) {
+            const uint64_t adv = (uint64_t)(kk * 32 >> 4);   // 16 bf16 = 32 bytes along K
+            mma_bf16_ts(d_tmem, a_lo0 + kk * 8, w_hi + adv, idesc, accumulate);   // small terms first
+            mma_bf16_ts(d_tmem, a_hi0 + kk * 8, w_lo + adv, idesc, 1);
+            mma_bf16_ts(d_tmem, a_hi0 + kk * 8, w_hi + adv, idesc, 1);
+            accumulate = 1;
+          }
+        }
+        mma_commit(smem_u32(&bar_full));
+      }
+      __syncwarp();
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == N_EPI_WARPS) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+template <int KIN>
+cudaError_t launch_kin(const LstmTcArgs& a, cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(lstm_tc_kernel<KIN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         Cfg<KIN>::SMEM);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  dim3 grid((a.nseq + TILE - 1) / TILE, a.ndir);
+  lstm_tc_kernel<KIN><<<grid, THREADS, Cfg<KIN>::SMEM, s>>>(a);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+cudaError_t launch_lstm_tc(const LstmTcArgs& a, cudaStream_t s) {
+  if (a.nseq <= 0 || a.nsteps <= 0) return cudaSuccess;
+  if (a.kin == 64) return launch_kin<64>(a, s);
+  if (a.kin == 128) return launch_kin<128>(a, s);
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace bsb
