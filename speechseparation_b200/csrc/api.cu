@@ -201,6 +201,9 @@ int bsb_pack_weights(const void* const* src, int n_src, void* packed, void* stre
         CK(launch_pack_lstm_tc(F(k), F(k + 1), F(k + 2), F(k + 3), layer == 0 ? F(I.rnn[j]) : nullptr,
                                layer == 0 ? F(I.rnn[j] + 1) : nullptr, ih.K, dst + R.tcw[layer][d],
                                dst + R.tcb[layer][d], s));
+        if (R.ndir == 1)
+          CK(launch_pack_lstm_seq(F(k), F(k + 1), F(k + 2), F(k + 3), layer == 0 ? F(I.rnn[j]) : nullptr,
+                                  layer == 0 ? F(I.rnn[j] + 1) : nullptr, dst + R.sqw[layer], dst + R.sqb[layer], s));
         k += 4;
       }
     }
@@ -309,6 +312,31 @@ int run_rnn_block(int j, const float* fin, int C, int T, const void* packed, con
       for (int d = 0; d < R.ndir; ++d) { a.wimg[d] = PW(packed, R.tcw[layer][d]); a.bias[d] = PW(packed, R.tcb[layer][d]); }
       a.nseq = C * T; a.nsteps = kBands; a.ndir = R.ndir;
       CK(launch_lstm_tc(a, s));
+      std::snprintf(nm, sizeof(nm), "rnn%d.rec%d", j, layer);
+      mark(nm, s);
+    }
+    CKI(single_linear(packed, R.fc, hl[1], ldh, fout, kFeat, rows, ACT_NONE, fin, kFeat, s));
+    std::snprintf(nm, sizeof(nm), "rnn%d.fc", j);
+    mark(nm, s);
+    return 0;
+  }
+  if (!band && T >= kLstmSeqMinSteps && !force_ffma()) {
+    // latency path: 8 sequences per CTA, fc_in and W_ih fused into the recurrence (lstm_seq.cu)
+    float* hl[2] = {w.hbuf, w.xproj};
+    for (int layer = 0; layer < 2; ++layer) {
+      LstmSeqArgs a{};
+      a.x = layer == 0 ? fin : hl[0];
+      a.hout = hl[layer];
+      a.wfrag = PW(packed, R.sqw[layer]);
+      a.bias = PW(packed, R.sqb[layer]);
+      a.nseq = C * kBands; a.nsteps = T; a.n_inner = kBands;
+      a.x_outer = a.h_outer = (long long)T * kBands * kFeat;
+      a.x_inner = a.h_inner = kFeat;
+      a.x_step = a.h_step = (long long)kBands * kFeat;
+      const long long per = (long long)a.nseq * kFeat;       // state [2(h,c)][2 layers][nseq][64]
+      if (st_in) { a.h0 = st_in + layer * per; a.c0 = st_in + (2 + layer) * per; }
+      if (st_out) { a.hN = st_out + layer * per; a.cN = st_out + (2 + layer) * per; }
+      CK(launch_lstm_seq(a, s));
       std::snprintf(nm, sizeof(nm), "rnn%d.rec%d", j, layer);
       mark(nm, s);
     }

@@ -80,6 +80,22 @@ struct LstmTcArgs {
   int nseq, nsteps, ndir, kin;
 };
 cudaError_t launch_lstm_tc(const LstmTcArgs& a, cudaStream_t s);
+// Time-axis LSTM layer with the input projection fused, 8 sequences per CTA on mma.sync (lstm_seq.cu).
+// Sequence addressing as LstmArgs: (seq / n_inner) * outer + (seq % n_inner) * inner + step * step.
+struct LstmSeqArgs {
+  const float* x;            // 64 input features per (seq, step)
+  float* hout;               // 64 outputs per (seq, step)
+  const void* wfrag;         // layout.h RnnBlock::sqw
+  const float* bias;         // RnnBlock::sqb
+  const float* h0;           // optional initial state [nseq][64]
+  const float* c0;
+  float* hN;                 // optional final state
+  float* cN;
+  long long x_outer, x_inner, x_step, h_outer, h_inner, h_step;
+  int n_inner, nseq, nsteps;
+};
+cudaError_t launch_lstm_seq(const LstmSeqArgs& a, cudaStream_t s);
+constexpr int kLstmSeqMinSteps = 2;  // single steps (streaming hops) stay on the FFMA recurrence
 constexpr int kLstmTcMinSeq = 128;   // below one full tile the FFMA recurrence is used
 int force_ffma();
 
@@ -115,5 +131,8 @@ cudaError_t launch_pack_bias(const float* b1, const float* b2, int N, float* dst
 cudaError_t launch_pack_lstm_tc(const float* w_ih, const float* w_hh, const float* b_ih, const float* b_hh,
                                 const float* w_in, const float* b_in, int kin, void* img, float* bias,
                                 cudaStream_t s);
+// mma.sync fragment image + bias for the time-axis kernel (RnnBlock::sqw/sqb), kin = 64
+cudaError_t launch_pack_lstm_seq(const float* w_ih, const float* w_hh, const float* b_ih, const float* b_hh,
+                                 const float* w_in, const float* b_in, void* img, float* bias, cudaStream_t s);
 
 }  // namespace bsb

@@ -57,6 +57,10 @@ Layout build_layout() {
         R.tcw[layer][d] = B.take(tc_lstm_img_floats(layer, R.ndir));
         R.tcb[layer][d] = B.take(kGates);
       }
+    for (int layer = 0; layer < 2; ++layer) {
+      R.sqw[layer] = R.ndir == 1 ? B.take(kSeqImgFloats) : -1;
+      R.sqb[layer] = R.ndir == 1 ? B.take(kGates) : -1;
+    }
   }
   for (int i = 0; i < kRealBands; ++i) {       // bandFCs_back, bsrnn.py:361-369
     int d = kBandD[i], h = imax(d, kMaskHidden);

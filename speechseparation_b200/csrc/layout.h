@@ -55,7 +55,12 @@ struct RnnBlock {
   //   tcb: fp32 [256] bias in the same row order and scaling.
   long long tcw[2][2];
   long long tcb[2][2];
+  // time-axis blocks (ndir == 1) only: per layer, the same matrix as mma.sync A fragments
+  // [warp 16][k-tile 8][plane 2][lane 32][4 words] and the bias [warp 16][16 rows] (lstm_seq.cu)
+  long long sqw[2];
+  long long sqb[2];
 };
+constexpr long long kSeqImgFloats = 16 * 8 * 2 * 32 * 4;
 inline constexpr int tc_lstm_kin(int layer, int ndir) { return layer == 0 ? kFeat : kFeat * ndir; }
 inline constexpr int tc_lstm_chunks(int layer, int ndir) { return (tc_lstm_kin(layer, ndir) + kFeat) / 64; }
 inline constexpr long long tc_lstm_img_floats(int layer, int ndir) {   // 2 planes x chunks x 256 x 64 bf16

@@ -34,18 +34,13 @@ __global__ void pack_split_kernel(const float* __restrict__ src, int N, int K, _
   }
 }
 
-// Tensor-core LSTM layer image (layout.h RnnBlock::tcw/tcb). Block n = 4*unit + gate, thread k of
-// the concatenated K axis [x part (kin) | h part (64)]. fc_in (bsrnn.py:69,80) is folded into the
-// layer-0 input weights in double precision: W_ih.(W_in.x + b_in) = (W_ih.W_in).x + W_ih.b_in.
-__global__ void pack_lstm_tc_kernel(const float* __restrict__ w_ih, const float* __restrict__ w_hh,
-                                    const float* __restrict__ b_ih, const float* __restrict__ b_hh,
-                                    const float* __restrict__ w_in, const float* __restrict__ b_in, int kin,
-                                    uint8_t* __restrict__ img, float* __restrict__ bias) {
-  const int n = blockIdx.x, k = threadIdx.x;
-  const int unit = n >> 2, gate = n & 3;
-  const int row = gate * kFeat + unit;                 // nn.LSTM row: gates stacked i,f,g,o
-  const double scale = (gate == 2 ? -2.0 : -1.0) * 1.4426950408889634;
-  const int nch = (kin + kFeat) / 64;
+// Element (row, k) of the concatenated LSTM matrix [W_ih' | W_hh] (row in nn.LSTM order, gates stacked
+// i,f,g,o), scaled by -log2(e) (i,f,o) or -2.log2(e) (g) so that the gate pre-activation is directly the
+// ex2 argument of the cell update. fc_in (bsrnn.py:69,80) is folded into the layer-0 input weights in
+// double precision: W_ih.(W_in.x + b_in) = (W_ih.W_in).x + W_ih.b_in.
+__device__ double lstm_gate_scale(int gate) { return (gate == 2 ? -2.0 : -1.0) * 1.4426950408889634; }
+__device__ float lstm_cat_weight(int row, int k, int kin, const float* __restrict__ w_ih,
+                                 const float* __restrict__ w_hh, const float* __restrict__ w_in) {
   double w;
   if (k < kin) {
     if (w_in != nullptr) {
@@ -57,7 +52,28 @@ __global__ void pack_lstm_tc_kernel(const float* __restrict__ w_ih, const float*
   } else {
     w = (double)w_hh[row * kFeat + (k - kin)];
   }
-  const float wf = (float)(w * scale);
+  return (float)(w * lstm_gate_scale(row / kFeat));
+}
+__device__ float lstm_cat_bias(int row, const float* __restrict__ w_ih, const float* __restrict__ b_ih,
+                               const float* __restrict__ b_hh, const float* __restrict__ w_in,
+                               const float* __restrict__ b_in) {
+  double b = (double)b_ih[row] + (double)b_hh[row];
+  if (w_in != nullptr)
+    for (int j = 0; j < kFeat; ++j) b += (double)w_ih[row * kFeat + j] * (double)b_in[j];
+  return (float)(b * lstm_gate_scale(row / kFeat));
+}
+
+// Tensor-core LSTM layer image (layout.h RnnBlock::tcw/tcb). Block n = 4*unit + gate, thread k of
+// the concatenated K axis [x part (kin) | h part (64)].
+__global__ void pack_lstm_tc_kernel(const float* __restrict__ w_ih, const float* __restrict__ w_hh,
+                                    const float* __restrict__ b_ih, const float* __restrict__ b_hh,
+                                    const float* __restrict__ w_in, const float* __restrict__ b_in, int kin,
+                                    uint8_t* __restrict__ img, float* __restrict__ bias) {
+  const int n = blockIdx.x, k = threadIdx.x;
+  const int unit = n >> 2, gate = n & 3;
+  const int row = gate * kFeat + unit;                 // nn.LSTM row: gates stacked i,f,g,o
+  const int nch = (kin + kFeat) / 64;
+  const float wf = lstm_cat_weight(row, k, kin, w_ih, w_hh, w_in);
   const __nv_bfloat16 h = __float2bfloat16_rn(wf);
   const __nv_bfloat16 l = __float2bfloat16_rn(wf - __bfloat162float(h));
   const int c = k >> 6, kk = k & 63;
@@ -65,12 +81,36 @@ __global__ void pack_lstm_tc_kernel(const float* __restrict__ w_ih, const float*
   const size_t plane = (size_t)nch * kGates * 128;
   *reinterpret_cast<__nv_bfloat16*>(img + off) = h;
   *reinterpret_cast<__nv_bfloat16*>(img + plane + off) = l;
-  if (k == 0) {
-    double b = (double)b_ih[row] + (double)b_hh[row];
-    if (w_in != nullptr)
-      for (int j = 0; j < kFeat; ++j) b += (double)w_ih[row * kFeat + j] * (double)b_in[j];
-    bias[n] = (float)(b * scale);
+  if (k == 0) bias[n] = lstm_cat_bias(row, w_ih, b_ih, b_hh, w_in, b_in);
+}
+
+// mma.sync fragment image of the same matrix for the time-axis kernel (lstm_seq.cu, kin = 64):
+// block (warp w, k-tile kt, plane p), thread (lane, reg): the m16n8k16 A fragment word `reg` of `lane`
+// for the 16 gate rows of warp w (rows 0-7: i,f of units 4w..4w+3 interleaved; rows 8-15: g,o).
+__device__ __forceinline__ int seq_row_of(int w, int rm) {
+  const int unit = 4 * w + ((rm & 7) >> 1);
+  const int gate = (rm < 8 ? 0 : 2) + (rm & 1);
+  return gate * kFeat + unit;
+}
+__global__ void pack_lstm_seq_kernel(const float* __restrict__ w_ih, const float* __restrict__ w_hh,
+                                     const float* __restrict__ b_ih, const float* __restrict__ b_hh,
+                                     const float* __restrict__ w_in, const float* __restrict__ b_in,
+                                     uint32_t* __restrict__ img, float* __restrict__ bias) {
+  const int w = blockIdx.x, kt = blockIdx.y, p = blockIdx.z;
+  const int lane = threadIdx.x >> 2, reg = threadIdx.x & 3;
+  const int rm = (lane >> 2) + ((reg & 1) ? 8 : 0);
+  const int k = kt * 16 + 2 * (lane & 3) + ((reg & 2) ? 8 : 0);
+  const int row = seq_row_of(w, rm);
+  float v[2];
+  for (int e = 0; e < 2; ++e) {
+    const float wf = lstm_cat_weight(row, k + e, kFeat, w_ih, w_hh, w_in);
+    const float hi = __bfloat162float(__float2bfloat16_rn(wf));
+    v[e] = p == 0 ? hi : wf - hi;
   }
+  const __nv_bfloat162 pk = __floats2bfloat162_rn(v[0], v[1]);
+  img[(((size_t)w * 8 + kt) * 2 + p) * 128 + lane * 4 + reg] = *reinterpret_cast<const uint32_t*>(&pk);
+  if (kt == 0 && p == 0 && threadIdx.x < 16)
+    bias[w * 16 + threadIdx.x] = lstm_cat_bias(seq_row_of(w, threadIdx.x), w_ih, b_ih, b_hh, w_in, b_in);
 }
 
 }  // namespace
@@ -80,6 +120,14 @@ cudaError_t launch_pack_lstm_tc(const float* w_ih, const float* w_hh, const floa
                                 cudaStream_t s) {
   pack_lstm_tc_kernel<<<kGates, kin + kFeat, 0, s>>>(w_ih, w_hh, b_ih, b_hh, w_in, b_in, kin,
                                                      reinterpret_cast<uint8_t*>(img), bias);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_pack_lstm_seq(const float* w_ih, const float* w_hh, const float* b_ih, const float* b_hh,
+                                 const float* w_in, const float* b_in, void* img, float* bias, cudaStream_t s) {
+  pack_lstm_seq_kernel<<<dim3(16, 8, 2), 128, 0, s>>>(w_ih, w_hh, b_ih, b_hh, w_in, b_in,
+                                                      reinterpret_cast<uint32_t*>(img), bias);
   count_launch();
   return cudaGetLastError();
 }
