@@ -21,16 +21,28 @@ __global__ void pack_bias_kernel(const float* __restrict__ b1, const float* __re
   if (i < N) dst[i] = b2 ? b1[i] + b2[i] : b1[i];
 }
 
-__global__ void pack_split_kernel(const float* __restrict__ src, int N, int K, __nv_bfloat16* __restrict__ hi,
-                                  __nv_bfloat16* __restrict__ lo, int ldd) {
+// W [N][K] fp32 -> bf16 hi/lo planes in the tensor-core kernel's shared-memory image: the plane is cut
+// into blocks of (up to) 256 rows x 64 k, each stored contiguously as [rows][128 B] with the
+// 16-byte chunks of a row XOR-swizzled by (row & 7) (UMMA SWIZZLE_128B, K-major), blocks ordered
+// n-tile major, k-chunk minor, so tc_linear.cu fetches a block with one cp.async.bulk.
+// ldd = K padded to 64; rows are padded to 64 (zeros come from the memset of the packed buffer).
+__global__ void pack_split_kernel(const float* __restrict__ src, int N, int K, uint8_t* __restrict__ hi,
+                                  uint8_t* __restrict__ lo, int ldd) {
   const long long total = (long long)N * K;
+  const int npad = (N + 63) / 64 * 64;
+  const int nch = ldd >> 6;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const int n = (int)(i / K), k = (int)(i - (long long)n * K);
     const float w = src[i];
     const __nv_bfloat16 h = __float2bfloat16_rn(w);
-    hi[(long long)n * ldd + k] = h;
-    lo[(long long)n * ldd + k] = __float2bfloat16_rn(w - __bfloat162float(h));
+    const __nv_bfloat16 l = __float2bfloat16_rn(w - __bfloat162float(h));
+    const int n0 = n & ~255, r = n & 255;
+    const int bn = min(256, npad - n0);
+    const int c = k >> 6, kk = k & 63;
+    const size_t off = ((size_t)n0 * nch + (size_t)c * bn + r) * 128 + (((kk >> 3) ^ (r & 7)) << 4) + (kk & 7) * 2;
+    *reinterpret_cast<__nv_bfloat16*>(hi + off) = h;
+    *reinterpret_cast<__nv_bfloat16*>(lo + off) = l;
   }
 }
 
@@ -137,8 +149,8 @@ cudaError_t launch_pack_split(const float* src, int N, int K, void* dst_hi, void
   if (total == 0) return cudaSuccess;
   int blocks = (int)((total + 255) / 256);
   if (blocks > 1184) blocks = 1184;
-  pack_split_kernel<<<blocks, 256, 0, s>>>(src, N, K, reinterpret_cast<__nv_bfloat16*>(dst_hi),
-                                           reinterpret_cast<__nv_bfloat16*>(dst_lo), ldd);
+  pack_split_kernel<<<blocks, 256, 0, s>>>(src, N, K, reinterpret_cast<uint8_t*>(dst_hi),
+                                           reinterpret_cast<uint8_t*>(dst_lo), ldd);
   count_launch();
   return cudaGetLastError();
 }

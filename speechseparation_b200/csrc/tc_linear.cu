@@ -9,11 +9,16 @@
 // which reproduces the fp32 path to ~1e-5 end to end at 3 bf16 MMAs per product.
 //
 // Persistent, warp-specialised CTA (one per SM), tiles of 128 rows x up to 256 columns:
-//   warps 0-3  A producers : fp32 global -> registers -> (hi, lo) bf16 -> 128B-swizzled smem
-//   warps 4-7  W producers : pre-split bf16 weight planes (L2 resident) -> swizzled smem
+//   warps 0-7  A producers : fp32 global -> registers (one K chunk ahead of the smem stage, so the
+//                            HBM latency overlaps the previous chunk) -> (hi, lo) bf16 -> 128B-swizzled smem
+//   W tiles                : the weights are packed as ready-made swizzled [bn x 64] bf16 blocks
+//                            (pack.cu), so one thread fetches a hi and a lo block per K chunk with
+//                            cp.async.bulk (TMA engine, completes on the stage's mbarrier)
 //   warp  8    MMA issuer  : one thread issues tcgen05.mma (M=128, N<=256, K=16) x 12 per 64-wide
 //                            K chunk; tcgen05.commit frees the smem stage / publishes the tile
-//   warps 9-12 epilogue    : tcgen05.ld TMEM -> registers, bias + LeakyReLU (+residual, *x), store
+//   warps 9-12 epilogue    : tcgen05.ld TMEM -> registers -> per-warp smem transpose, then bias +
+//                            LeakyReLU (+residual, *x) on rows of 32 consecutive columns so that every
+//                            global load/store of the epilogue is a full 128-byte line
 // Two smem stages (mbarrier full/empty ring) and two 256-column TMEM accumulators (full/empty
 // barriers) let producer, tensor core and epilogue overlap across K chunks and across tiles.
 #include "kernels.cuh"
@@ -31,12 +36,13 @@ constexpr int STAGES = 2;
 constexpr int A_PLANE = BM * 128;            // bytes of one A plane per stage (16 KB)
 constexpr int W_PLANE = BN_MAX * 128;        // bytes of one W plane per stage (32 KB)
 constexpr int STAGE_BYTES = 2 * A_PLANE + 2 * W_PLANE;   // 96 KB
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024;  // + alignment slack
-constexpr int N_A_WARPS = 4, N_W_WARPS = 4, N_EPI_WARPS = 4;
-constexpr int MMA_WARP = N_A_WARPS + N_W_WARPS;          // 8
-constexpr int EPI_WARP0 = MMA_WARP + 1;                  // 9
-constexpr int THREADS = (N_A_WARPS + N_W_WARPS + 1 + N_EPI_WARPS) * 32;   // 416
-constexpr int N_PRODUCERS = (N_A_WARPS + N_W_WARPS) * 32;                 // 256
+constexpr int STG_LD = 36;                              // staging row stride (floats): conflict-free 16B access
+constexpr int STG_WARP = 32 * STG_LD * 4;               // bytes of one epilogue warp's 32x32 staging tile
+constexpr int N_A_WARPS = 8, N_EPI_WARPS = 4;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + N_EPI_WARPS * STG_WARP + 1024;  // + alignment slack
+constexpr int MMA_WARP = N_A_WARPS;                      // 8
+constexpr int THREADS = (N_A_WARPS + 1 + N_EPI_WARPS) * 32;   // 416
+constexpr int N_PRODUCERS = N_A_WARPS * 32;                   // 256
 constexpr int TMEM_COLS = 512;       // 2 accumulators x 256 fp32 columns
 
 struct TcProb {
@@ -79,12 +85,14 @@ __device__ __forceinline__ Tile decode_tile(const TcArgs& args, int tile) {
 __device__ __forceinline__ uint32_t sw128(int r, int c) { return (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4)); }
 
 // ---- A producer: 128 rows x 64 k of fp32 -> hi/lo bf16 planes --------------------------------
-__device__ __forceinline__ void produce_a(const TcProb& P, int m0, int k0, uint8_t* a_hi, uint8_t* a_lo, int t) {
+// 256 threads; thread t owns the 8-float groups g = t + 256 i (row g/8, 16-byte chunk g%8), i < 4.
+struct AChunk { float4 v[4][2]; };
+
+__device__ __forceinline__ void load_a(const TcProb& P, int m0, int k0, int t, AChunk& a) {
   const bool vec = ((P.lda & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.A) & 15) == 0);
-  float4 v[8][2];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int g = t + 128 * i;          // 8-float group: row g/8, chunk g%8
+  for (int i = 0; i < 4; ++i) {
+    const int g = t + 256 * i;
     const int r = g >> 3, c = g & 7;
     const int m = m0 + r, k = k0 + c * 8;
     float4 x0 = make_float4(0.f, 0.f, 0.f, 0.f), x1 = x0;
@@ -101,38 +109,24 @@ __device__ __forceinline__ void produce_a(const TcProb& P, int m0, int k0, uint8
         x1 = make_float4(e[4], e[5], e[6], e[7]);
       }
     }
-    v[i][0] = x0;
-    v[i][1] = x1;
-  }
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int g = t + 128 * i;
-    const int r = g >> 3, c = g & 7;
-    uint4 h, l;
-    split2(v[i][0].x, v[i][0].y, h.x, l.x);
-    split2(v[i][0].z, v[i][0].w, h.y, l.y);
-    split2(v[i][1].x, v[i][1].y, h.z, l.z);
-    split2(v[i][1].z, v[i][1].w, h.w, l.w);
-    const uint32_t off = sw128(r, c);
-    *reinterpret_cast<uint4*>(a_hi + off) = h;
-    *reinterpret_cast<uint4*>(a_lo + off) = l;
+    a.v[i][0] = x0;
+    a.v[i][1] = x1;
   }
 }
 
-// ---- W producer: bn rows x 64 k of pre-split bf16 (two planes) ------------------------------------
-__device__ __forceinline__ void produce_w(const TcProb& P, int n0, int bn, int k0, uint8_t* w_hi, uint8_t* w_lo, int t) {
-  const int groups = bn * 8;            // 16-byte chunks per plane
-  const __nv_bfloat16* gh = P.Wh + (long long)n0 * P.ldw + k0;
-  const __nv_bfloat16* gl = P.Wl + (long long)n0 * P.ldw + k0;
-#pragma unroll 4
-  for (int g = t; g < groups; g += 128) {
+__device__ __forceinline__ void store_a(const AChunk& a, uint8_t* a_hi, uint8_t* a_lo, int t) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int g = t + 256 * i;
     const int r = g >> 3, c = g & 7;
-    const long long src = (long long)r * P.ldw + c * 8;
-    const uint4 h = __ldg(reinterpret_cast<const uint4*>(gh + src));
-    const uint4 l = __ldg(reinterpret_cast<const uint4*>(gl + src));
+    uint4 h, l;
+    split2(a.v[i][0].x, a.v[i][0].y, h.x, l.x);
+    split2(a.v[i][0].z, a.v[i][0].w, h.y, l.y);
+    split2(a.v[i][1].x, a.v[i][1].y, h.z, l.z);
+    split2(a.v[i][1].z, a.v[i][1].w, h.w, l.w);
     const uint32_t off = sw128(r, c);
-    *reinterpret_cast<uint4*>(w_hi + off) = h;
-    *reinterpret_cast<uint4*>(w_lo + off) = l;
+    *reinterpret_cast<uint4*>(a_hi + off) = h;
+    *reinterpret_cast<uint4*>(a_lo + off) = l;
   }
 }
 
@@ -152,7 +146,7 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
 
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) {
-      mbar_init(smem_u32(&bar_full[s]), N_PRODUCERS);
+      mbar_init(smem_u32(&bar_full[s]), N_PRODUCERS + 1);   // + the W issuer's expect_tx arrive
       mbar_init(smem_u32(&bar_empty[s]), 1);
     }
     for (int a = 0; a < 2; ++a) {
@@ -172,23 +166,43 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
 
   if (warp < MMA_WARP) {
     // ================= producers =================
-    const bool is_a = warp < N_A_WARPS;
-    const int t = is_a ? tid : tid - N_A_WARPS * 32;
     int stage = 0;
     uint32_t phase = 0;
-    for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
-      const Tile T = decode_tile(args, tile);
+    int tile = blockIdx.x, kc = 0, nk = 0;
+    Tile T{};
+    AChunk regs;
+    if (tile < args.total_tiles) {
+      T = decode_tile(args, tile);
+      nk = (args.p[T.pi].K + BK - 1) / BK;
+      load_a(args.p[T.pi], T.m0, 0, tid, regs);
+    }
+    while (tile < args.total_tiles) {
       const TcProb& P = args.p[T.pi];
-      const int nk = (P.K + BK - 1) / BK;
-      for (int kc = 0; kc < nk; ++kc) {
-        mbar_wait(smem_u32(&bar_empty[stage]), phase ^ 1);
-        uint8_t* sb = smem_gen + stage * STAGE_BYTES;
-        if (is_a) produce_a(P, T.m0, kc * BK, sb, sb + A_PLANE, t);
-        else produce_w(P, T.n0, T.bn, kc * BK, sb + 2 * A_PLANE, sb + 2 * A_PLANE + W_PLANE, t);
-        fence_proxy_async_smem();
-        mbar_arrive(smem_u32(&bar_full[stage]));
-        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      mbar_wait(smem_u32(&bar_empty[stage]), phase ^ 1);
+      uint8_t* sb = smem_gen + stage * STAGE_BYTES;
+      if (tid == 0) {
+        // W blocks [bn x 64] bf16, already swizzled: (n0 * nch + kc * bn) * 128 bytes into each plane
+        const uint32_t bytes = (uint32_t)T.bn * 128u;
+        const long long off = ((long long)T.n0 * (P.ldw >> 6) + (long long)kc * T.bn) * 128;
+        const uint32_t bar = smem_u32(&bar_full[stage]);
+        mbar_arrive_expect_tx(bar, 2 * bytes);
+        bulk_g2s(smem_base + stage * STAGE_BYTES + 2 * A_PLANE, reinterpret_cast<const uint8_t*>(P.Wh) + off, bytes, bar);
+        bulk_g2s(smem_base + stage * STAGE_BYTES + 2 * A_PLANE + W_PLANE, reinterpret_cast<const uint8_t*>(P.Wl) + off, bytes, bar);
       }
+      store_a(regs, sb, sb + A_PLANE, tid);
+      fence_proxy_async_smem();
+      mbar_arrive(smem_u32(&bar_full[stage]));
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      // next chunk: its global loads fly while the tensor core works on the stage just filled
+      if (++kc == nk) {
+        kc = 0;
+        tile += gridDim.x;
+        if (tile < args.total_tiles) {
+          T = decode_tile(args, tile);
+          nk = (args.p[T.pi].K + BK - 1) / BK;
+        }
+      }
+      if (tile < args.total_tiles) load_a(args.p[T.pi], T.m0, kc * BK, tid, regs);
     }
   } else if (warp == MMA_WARP) {
     // ================= MMA issuer =================
@@ -229,6 +243,8 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
   } else {
     // ================= epilogue =================
     const int q = warp & 3;                 // TMEM lane quarter this warp may access
+    float* stg = reinterpret_cast<float*>(smem_gen + STAGES * STAGE_BYTES + (warp - MMA_WARP - 1) * STG_WARP);
+    const int cg = lane & 7, sub = lane >> 3;   // transposed phase: 4 columns at 4*cg of rows sub + 4k
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
@@ -236,59 +252,85 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
       const TcProb& P = args.p[T.pi];
       mbar_wait(smem_u32(&bar_tfull[acc]), acc_phase);
       tc_fence_after();
-      const int m = T.m0 + q * 32 + lane;
-      const bool row_ok = m < P.M;
-      float* orow = P.O + (long long)m * P.ldo;
-      const float* rrow = P.res ? P.res + (long long)m * P.ldres : nullptr;
-      const float* mrow = P.mul ? P.mul + (long long)m * P.ldmul : nullptr;
+      const int mw = T.m0 + q * 32;           // first row of this warp
       const bool o_vec = ((P.ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.O) & 15) == 0);
-      const bool r_vec = rrow && ((P.ldres & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.res) & 15) == 0);
-      const bool m_vec = mrow && ((P.ldmul & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.mul) & 15) == 0);
+      const bool r_vec = P.res && ((P.ldres & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.res) & 15) == 0);
+      const bool m_vec = P.mul && ((P.ldmul & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.mul) & 15) == 0);
       const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN_MAX);
       for (int cc = 0; cc < T.bn / 32; ++cc) {
+        const int nb = T.n0 + cc * 32;
+        if (nb >= P.N) break;
+        // operands of the fused "+ residual" / "* x": all loads of the chunk are issued up front
+        const int n = nb + 4 * cg;
+        const bool ncol = n < P.N;
+        const bool full4 = n + 3 < P.N;
+        float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 rr[8], mm[8];
+        if (ncol) bb = __ldg(reinterpret_cast<const float4*>(P.bias + n));   // bias padded to Npad
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int m = mw + sub + 4 * k;
+          rr[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+          mm[k] = make_float4(1.f, 1.f, 1.f, 1.f);
+          if (ncol && m < P.M) {
+            if (P.res) {
+              const float* rrow = P.res + (long long)m * P.ldres + n;
+              if (r_vec && full4) {
+                rr[k] = __ldg(reinterpret_cast<const float4*>(rrow));
+              } else {
+                rr[k].x = __ldg(rrow);
+                if (n + 1 < P.N) rr[k].y = __ldg(rrow + 1);
+                if (n + 2 < P.N) rr[k].z = __ldg(rrow + 2);
+                if (n + 3 < P.N) rr[k].w = __ldg(rrow + 3);
+              }
+            }
+            if (P.mul) {
+              const float* mrow = P.mul + (long long)m * P.ldmul + n;
+              if (m_vec && full4) {
+                mm[k] = __ldg(reinterpret_cast<const float4*>(mrow));
+              } else {
+                mm[k].x = __ldg(mrow);
+                if (n + 1 < P.N) mm[k].y = __ldg(mrow + 1);
+                if (n + 2 < P.N) mm[k].z = __ldg(mrow + 2);
+                if (n + 3 < P.N) mm[k].w = __ldg(mrow + 3);
+              }
+            }
+          }
+        }
         uint32_t r[32];
         tmem_ld_32x32(tbase + cc * 32, r);
         tmem_ld_wait();
-        const int nb = T.n0 + cc * 32;
-        if (row_ok && nb < P.N) {
 #pragma unroll
-          for (int j4 = 0; j4 < 8; ++j4) {
-            const int n = nb + j4 * 4;
-            if (n >= P.N) break;
-            const float4 bb = __ldg(reinterpret_cast<const float4*>(P.bias + n));   // bias padded to Npad
-            float v[4] = {__uint_as_float(r[j4 * 4 + 0]) + bb.x, __uint_as_float(r[j4 * 4 + 1]) + bb.y,
-                          __uint_as_float(r[j4 * 4 + 2]) + bb.z, __uint_as_float(r[j4 * 4 + 3]) + bb.w};
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4*>(stg + lane * STG_LD + 4 * j) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+        __syncwarp();
+        if (ncol) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const int i = sub + 4 * k;
+            const int m = mw + i;
+            const float4 a4 = *reinterpret_cast<const float4*>(stg + i * STG_LD + 4 * cg);
+            float v[4] = {a4.x + bb.x, a4.y + bb.y, a4.z + bb.z, a4.w + bb.w};
             if (P.act == ACT_LRELU) {
 #pragma unroll
               for (int e = 0; e < 4; ++e) v[e] = lrelu(v[e]);
             }
-            const bool full4 = n + 3 < P.N;
-            if (rrow) {
-              if (r_vec && full4) {
-                const float4 x = __ldg(reinterpret_cast<const float4*>(rrow + n));
-                v[0] += x.x; v[1] += x.y; v[2] += x.z; v[3] += x.w;
+            v[0] = (v[0] + rr[k].x) * mm[k].x;
+            v[1] = (v[1] + rr[k].y) * mm[k].y;
+            v[2] = (v[2] + rr[k].z) * mm[k].z;
+            v[3] = (v[3] + rr[k].w) * mm[k].w;
+            if (m < P.M) {
+              float* orow = P.O + (long long)m * P.ldo + n;
+              if (o_vec && full4) {
+                *reinterpret_cast<float4*>(orow) = make_float4(v[0], v[1], v[2], v[3]);
               } else {
 #pragma unroll
-                for (int e = 0; e < 4; ++e) if (n + e < P.N) v[e] += __ldg(rrow + n + e);
+                for (int e = 0; e < 4; ++e) if (n + e < P.N) orow[e] = v[e];
               }
-            }
-            if (mrow) {
-              if (m_vec && full4) {
-                const float4 x = __ldg(reinterpret_cast<const float4*>(mrow + n));
-                v[0] *= x.x; v[1] *= x.y; v[2] *= x.z; v[3] *= x.w;
-              } else {
-#pragma unroll
-                for (int e = 0; e < 4; ++e) if (n + e < P.N) v[e] *= __ldg(mrow + n + e);
-              }
-            }
-            if (o_vec && full4) {
-              *reinterpret_cast<float4*>(orow + n) = make_float4(v[0], v[1], v[2], v[3]);
-            } else {
-#pragma unroll
-              for (int e = 0; e < 4; ++e) if (n + e < P.N) orow[n + e] = v[e];
             }
           }
         }
+        __syncwarp();
       }
       tc_fence_before();
       mbar_arrive(smem_u32(&bar_tempty[acc]));

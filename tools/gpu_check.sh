@@ -1,0 +1,8 @@
+timeout 300 python -m pytest tests -m gpu -x -q 2>&1 | tail -8
+python bench.py --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/bcur.log 2>&1
+python - <<PY
+import json
+d=json.loads(open("gpurun_out/bcur.log").read().strip().splitlines()[-1])
+print(d["ms_per_step"], d["value"], d["e2e"]["value"])
+print(" ".join(f"{k}={v['ms']:.3f}" for k,v in d["stages"].items()))
+PY
