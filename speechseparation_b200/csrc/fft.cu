@@ -1,10 +1,11 @@
 // STFT / iSTFT for the model's fixed framing: n_fft 2048, hop 1024, periodic Hann.
 //
-// A 2048-point real transform is done as one 1024-point complex Stockham radix-4 FFT in
-// shared memory (5 passes, 256 threads = one butterfly each per pass) plus an O(N) split
-// step, one frame per CTA.  Window multiply and reflect padding are fused into the load,
-// the Re/Im interleave of m_dataset.py:189-190 into the store.  Twiddles come from tables
-// computed in double precision on the host.
+// A 2048-point real transform is done as one 1024-point complex FFT plus an O(N) split step.
+// Offline (throughput) kernels: one warp per frame, two in-register 32-point FFTs around one
+// shared-memory transpose. Streaming (latency) kernels: one CTA per row, Stockham radix-4 in
+// shared memory (5 passes, 256 threads). Window multiply and reflect padding are fused into
+// the load, the Re/Im interleave of m_dataset.py:189-190 into the store. Twiddles come from
+// tables computed in double precision on the host.
 //
 //   analysis  : torch.stft(center=True, pad_mode="reflect", onesided, unnormalised)
 //               (m_dataset.py:188; infer.py:31)  and torch.fft.rfft(buf*win) (infer-streaming.py:119)
@@ -91,75 +92,192 @@ __device__ __forceinline__ void irfft_split_load(const float* in, const float2* 
 }
 
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kFftThreads)
-stft_frames_kernel(const float* __restrict__ wav, long long L, int T, const float* __restrict__ win,
-                   const float2* __restrict__ tw, float* __restrict__ xf, int xs) {
-  __shared__ __align__(16) float2 sa[kM];
-  __shared__ __align__(16) float2 sb[kM];
-  const int r = blockIdx.x;              // frame-row c*T + t
-  const int c = r / T, t = r - c * T;
-  const float* w0 = wav + (long long)c * L;
-  const long long base = (long long)t * kHop - kHop;   // centre padding of n_fft/2
-  for (int n = threadIdx.x; n < kM; n += kFftThreads) {
-    float v[2];
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      long long j = base + 2 * n + e;
-      if (j < 0) j = -j;                                   // reflect (no edge repeat)
-      if (j >= L) j = 2 * (L - 1) - j;
-      v[e] = __ldg(w0 + j) * __ldg(win + 2 * n + e);
-    }
-    sa[n] = make_float2(v[0], v[1]);
+// Offline path: one WARP per frame. 1024 = 32 x 32: every lane runs a 32-point FFT in registers,
+// the warp transposes once through (padded) shared memory, every lane runs a second 32-point
+// FFT. No block barrier, 16 KB of smem traffic per frame instead of ~100 KB, and every global
+// access is a 256-byte run of consecutive lanes: the kernels are bound by HBM.
+//   z[n], n = l + 32 j ;  k = k1 + 32 k2 :
+//   X[k1 + 32 k2] = sum_l W32^(l k2) * ( W1024^(l k1) * sum_j z[l + 32 j] W32^(j k1) )
+constexpr int kFrameWarps = 4;                 // frames (warps) per CTA
+constexpr int kTr = 33;                        // transpose row stride (float2)
+
+__device__ __forceinline__ constexpr int br5(int i) {
+  return ((i & 1) << 4) | ((i & 2) << 2) | (i & 4) | ((i & 8) >> 2) | ((i & 16) >> 4);
+}
+__device__ __forceinline__ float cos32(int m) {   // cos(2 pi m / 32), m = 1..15 (folds after unrolling)
+  switch (m) {
+    case 1: return 0.98078528040323043f;  case 2: return 0.92387953251128674f;
+    case 3: return 0.83146961230254524f;  case 4: return 0.70710678118654752f;
+    case 5: return 0.55557023301960223f;  case 6: return 0.38268343236508977f;
+    case 7: return 0.19509032201612827f;  case 8: return 0.f;
+    case 9: return -0.19509032201612827f; case 10: return -0.38268343236508977f;
+    case 11: return -0.55557023301960223f; case 12: return -0.70710678118654752f;
+    case 13: return -0.83146961230254524f; case 14: return -0.92387953251128674f;
+    case 15: return -0.98078528040323043f; default: return 1.f;
   }
-  __syncthreads();
-  const float2* Z = fft1024<false>(sa, sb, tw);
-  rfft_split_store(Z, tw + kM, xf + (long long)r * xs);
+}
+__device__ __forceinline__ float sin32(int m) { return m <= 8 ? cos32(8 - m) : cos32(m - 8); }   // sin x = cos(x - pi/2)
+
+// in-register 32-point DIF FFT; result X[br5(i)] = v[i]. INV: conjugate twiddles, unnormalised.
+template <bool INV>
+__device__ __forceinline__ void fft32(float2 (&v)[32]) {
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) {
+#pragma unroll
+    for (int b = 0; b < 32; b += 2 * s) {
+#pragma unroll
+      for (int k = 0; k < s; ++k) {
+        const float2 a = v[b + k], c = v[b + k + s];
+        v[b + k] = make_float2(a.x + c.x, a.y + c.y);
+        const float2 d = make_float2(a.x - c.x, a.y - c.y);
+        const int m = k * (16 / s);
+        if (m == 0) {
+          v[b + k + s] = d;
+        } else if (m == 8) {
+          v[b + k + s] = INV ? make_float2(-d.y, d.x) : make_float2(d.y, -d.x);
+        } else {
+          const float cs = cos32(m), sn = sin32(m);
+          v[b + k + s] = INV ? make_float2(d.x * cs - d.y * sn, d.y * cs + d.x * sn)
+                             : make_float2(d.x * cs + d.y * sn, d.y * cs - d.x * sn);
+        }
+      }
+    }
+  }
 }
 
-// One CTA produces `blocks_per_cta` consecutive 1024-sample output blocks of one row.
-// Output block b (samples [1024b, 1024b+1024) of the trimmed signal) = second half of frame b
-// + first half of frame b+1, each irfft'ed and multiplied by the window, divided by
-// w^2[i] + w^2[i+1024] (torch.istft's window envelope; every kept sample has both frames).
-__global__ void __launch_bounds__(kFftThreads)
-istft_frames_kernel(const float* __restrict__ xf, int xs, int T, const float* __restrict__ win,
-                    const float2* __restrict__ tw, float* __restrict__ wav, int blocks_per_cta) {
-  __shared__ __align__(16) float2 sa[kM];
-  __shared__ __align__(16) float2 sb[kM];
-  __shared__ float prev[kHop];           // windowed second half of the previous frame
-  const int c = blockIdx.y;
-  const int b0 = blockIdx.x * blocks_per_cta;
-  const int nb = min(blocks_per_cta, (T - 1) - b0);
+// v[j] = z[lane + 32 j] on entry; v[br5(k2)] = Z[lane + 32 k2] on return
+template <bool INV>
+__device__ __forceinline__ void warp_fft1024(float2 (&v)[32], float2* tr, const float2* __restrict__ tw, int lane) {
+  fft32<INV>(v);
+#pragma unroll
+  for (int k1 = 0; k1 < 32; ++k1) {
+    float2 y = v[br5(k1)];
+    if (k1 > 0) {
+      float2 w = __ldg(tw + lane * k1);
+      if (INV) w.y = -w.y;
+      y = cmul(y, w);
+    }
+    tr[k1 * kTr + lane] = y;
+  }
+  __syncwarp();
+#pragma unroll
+  for (int l = 0; l < 32; ++l) v[l] = tr[lane * kTr + l];
+  __syncwarp();
+  fft32<INV>(v);
+}
+
+__global__ void __launch_bounds__(kFrameWarps * 32, 4)
+stft_warp_kernel(const float* __restrict__ wav, long long L, int T, int nrows, const float* __restrict__ win,
+                 const float2* __restrict__ tw, float* __restrict__ xf, int xs) {
+  __shared__ __align__(16) float2 tr_all[kFrameWarps][32 * kTr];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int r = blockIdx.x * kFrameWarps + warp;          // frame-row c*T + t
+  if (r >= nrows) return;                                  // warp-uniform; no block barrier below
+  const int c = r / T, t = r - c * T;
+  const float* w0 = wav + (long long)c * L;
+  const long long base = (long long)t * kHop - kHop;       // centre padding of n_fft/2
+  float2 v[32];
+  const bool fast = base >= 0 && base + kN <= L && ((reinterpret_cast<uintptr_t>(w0 + base) & 7) == 0);
+  if (fast) {
+    const float2* p = reinterpret_cast<const float2*>(w0 + base);
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const float2 x = __ldg(p + lane + 32 * j);
+      const float2 w = __ldg(reinterpret_cast<const float2*>(win) + lane + 32 * j);
+      v[j] = make_float2(x.x * w.x, x.y * w.y);
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const int n = lane + 32 * j;
+      float e[2];
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        long long i = base + 2 * n + q;
+        if (i < 0) i = -i;                                 // reflect (no edge repeat)
+        if (i >= L) i = 2 * (L - 1) - i;
+        e[q] = __ldg(w0 + i) * __ldg(win + 2 * n + q);
+      }
+      v[j] = make_float2(e[0], e[1]);
+    }
+  }
+  warp_fft1024<false>(v, tr_all[warp], tw, lane);
+  // split step: X[k] = E + W2048^k O with Z[k], Z[1024-k]; lane holds k = lane + 32 k2
+  float* out = xf + (long long)r * xs;
+  const float2* tw2 = tw + kM;
+  const int partner = (32 - lane) & 31;
+#pragma unroll
+  for (int k2 = 0; k2 < 32; ++k2) {
+    const float2 zk = v[br5(k2)];
+    const float2 pv = v[br5(31 - k2)];
+    float2 zm = make_float2(__shfl_sync(0xffffffffu, pv.x, partner), __shfl_sync(0xffffffffu, pv.y, partner));
+    if (lane == 0) zm = v[br5((32 - k2) & 31)];
+    const int k = lane + 32 * k2;
+    const float2 e = make_float2(0.5f * (zk.x + zm.x), 0.5f * (zk.y - zm.y));
+    const float2 o = make_float2(0.5f * (zk.y + zm.y), -0.5f * (zk.x - zm.x));
+    const float2 wo = cmul(__ldg(tw2 + k), o);
+    *reinterpret_cast<float2*>(out + 2 * k) = make_float2(e.x + wo.x, e.y + wo.y);
+  }
+  if (lane == 0) *reinterpret_cast<float2*>(out + 2 * kM) = make_float2(v[0].x - v[0].y, 0.f);
+}
+
+// A warp produces `per` consecutive 1024-sample output blocks of one row; the windowed second
+// half of the previous frame stays in registers (same lane, same slot as the next first half).
+__global__ void __launch_bounds__(kFrameWarps * 32, 4)
+istft_warp_kernel(const float* __restrict__ xf, int xs, int T, int nseg, int nwork, const float* __restrict__ win,
+                  const float2* __restrict__ tw, float* __restrict__ wav, int per) {
+  __shared__ __align__(16) float2 tr_all[kFrameWarps][32 * kTr];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int wk = blockIdx.x * kFrameWarps + warp;          // (row, segment)
+  if (wk >= nwork) return;
+  const int c = wk / nseg, b0 = (wk - c * nseg) * per;
+  const int nb = min(per, (T - 1) - b0);
   if (nb <= 0) return;
   const long long out_len = (long long)kHop * (T - 1);
   const float inv_m = 1.0f / kM;
+  const float2* tw2 = tw + kM;
+  const float2* win2 = reinterpret_cast<const float2*>(win);
+  float2 prev[16];
+  float2 v[32];
   for (int f = 0; f <= nb; ++f) {
     const int t = b0 + f;
-    irfft_split_load(xf + ((long long)c * T + t) * xs, tw + kM, sa);
-    __syncthreads();
-    const float2* z = fft1024<true>(sa, sb, tw);
-    // z[n] * inv_m = (x[2n], x[2n+1]); first half = n < 512, second half = n >= 512
+    const float* in = xf + ((long long)c * T + t) * xs;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const int k = lane + 32 * j;
+      float2 xk = __ldg(reinterpret_cast<const float2*>(in + 2 * k));
+      float2 xm = __ldg(reinterpret_cast<const float2*>(in + 2 * (kM - k)));
+      if (k == 0) { xk.y = 0.f; xm.y = 0.f; }
+      const float2 e = make_float2(0.5f * (xk.x + xm.x), 0.5f * (xk.y - xm.y));
+      const float2 dlt = make_float2(0.5f * (xk.x - xm.x), 0.5f * (xk.y + xm.y));
+      float2 w = __ldg(tw2 + k);
+      w.y = -w.y;
+      const float2 o = cmul(dlt, w);
+      v[j] = make_float2(e.x - o.y, e.y + o.x);
+    }
+    warp_fft1024<true>(v, tr_all[warp], tw, lane);
+    // v[br5(k2)] / 1024 = (x[2n], x[2n+1]), n = lane + 32 k2; k2 < 16 is the first half of the frame
     if (f > 0) {
       float* o = wav + (long long)c * out_len + (long long)(t - 1) * kHop;
-      for (int n = threadIdx.x; n < kM / 2; n += kFftThreads) {
-        const float2 v = z[n];
-        const int i = 2 * n;
-        const float w0 = __ldg(win + i), w1 = __ldg(win + i + 1);
-        const float u0 = __ldg(win + i + kHop), u1 = __ldg(win + i + 1 + kHop);
-        const float y0 = (prev[i] + v.x * inv_m * w0) / (u0 * u0 + w0 * w0);
-        const float y1 = (prev[i + 1] + v.y * inv_m * w1) / (u1 * u1 + w1 * w1);
-        *reinterpret_cast<float2*>(o + i) = make_float2(y0, y1);
+#pragma unroll
+      for (int k2 = 0; k2 < 16; ++k2) {
+        const int n = lane + 32 * k2;
+        const float2 z = v[br5(k2)];
+        const float2 w = __ldg(win2 + n), u = __ldg(win2 + n + kHop / 2);
+        const float y0 = __fdividef(fmaf(z.x * inv_m, w.x, prev[k2].x), fmaf(u.x, u.x, w.x * w.x));
+        const float y1 = __fdividef(fmaf(z.y * inv_m, w.y, prev[k2].y), fmaf(u.y, u.y, w.y * w.y));
+        *reinterpret_cast<float2*>(o + 2 * n) = make_float2(y0, y1);
       }
-      __syncthreads();                   // prev consumed before it is overwritten
     }
     if (f < nb) {
-      for (int n = threadIdx.x; n < kM / 2; n += kFftThreads) {
-        const float2 v = z[n + kM / 2];
-        const int i = 2 * n;
-        prev[i] = v.x * inv_m * __ldg(win + kHop + i);
-        prev[i + 1] = v.y * inv_m * __ldg(win + kHop + i + 1);
+#pragma unroll
+      for (int k2 = 0; k2 < 16; ++k2) {
+        const int n = lane + 32 * k2;
+        const float2 z = v[br5(k2 + 16)];
+        const float2 u = __ldg(win2 + n + kHop / 2);
+        prev[k2] = make_float2(z.x * inv_m * u.x, z.y * inv_m * u.y);
       }
     }
-    __syncthreads();                     // z (smem) is reused by the next frame's load
   }
 }
 
@@ -320,7 +438,8 @@ const float2* twiddle_tables(cudaStream_t, cudaError_t* err) {
 cudaError_t launch_stft_frames(const float* wav, int C, long long L, int T, const float* window,
                                float* xf, int xs, cudaStream_t s) {
   BSB_TABLES(window, tw);
-  stft_frames_kernel<<<C * T, kFftThreads, 0, s>>>(wav, L, T, window, tw, xf, xs);
+  const int nrows = C * T;
+  stft_warp_kernel<<<(nrows + kFrameWarps - 1) / kFrameWarps, kFrameWarps * 32, 0, s>>>(wav, L, T, nrows, window, tw, xf, xs);
   count_launch();
   return cudaGetLastError();
 }
@@ -329,12 +448,17 @@ cudaError_t launch_istft_frames(const float* xf, int xs, int C, int T, const flo
                                 float* wav, cudaStream_t s) {
   if (T < 2) return cudaSuccess;
   BSB_TABLES(window, tw);
-  // enough CTAs for >= 2 waves of 148 SMs x 4 resident CTAs when the clip allows it
-  int per = ((long long)(T - 1) * C + 1183) / 1184;
+  // a warp walks `per` consecutive output blocks (one extra frame of overlap per warp). Sized so
+  // that all warps are resident at once (148 SMs x 16 warps) when the input allows it: one
+  // balanced wave and <= 1/per redundant transforms.
+  const long long blocks = (long long)C * (T - 1);
+  int per = (int)((blocks + 148 * 16 - 1) / (148 * 16));
   if (per < 1) per = 1;
-  if (per > 64) per = 64;
-  dim3 grid((T - 1 + per - 1) / per, C);
-  istft_frames_kernel<<<grid, kFftThreads, 0, s>>>(xf, xs, T, window, tw, wav, per);
+  if (per > 32) per = 32;
+  const int nseg = (T - 1 + per - 1) / per;
+  const int nwork = C * nseg;
+  istft_warp_kernel<<<(nwork + kFrameWarps - 1) / kFrameWarps, kFrameWarps * 32, 0, s>>>(xf, xs, T, nseg, nwork, window, tw,
+                                                                                      wav, per);
   count_launch();
   return cudaGetLastError();
 }
