@@ -93,9 +93,10 @@ lstm_seq_kernel(const __grid_constant__ LstmSeqArgs a) {
       h0 = __ldg(a.h0 + (long long)gseq * kFeat + unit);
       c = __ldg(a.c0 + (long long)gseq * kFeat + unit);
     }
-    const __nv_bfloat16 hh = __float2bfloat16_rn(h0);
-    hB[0][0][sl][unit] = hh;
-    hB[0][1][sl][unit] = __float2bfloat16_rn(h0 - __bfloat162float(hh));
+    uint16_t hh, hl;
+    split1(h0, hh, hl);
+    reinterpret_cast<uint16_t&>(hB[0][0][sl][unit]) = hh;
+    reinterpret_cast<uint16_t&>(hB[0][1][sl][unit]) = hl;
   }
 
   // x loader / h writer role of the first 128 threads: (sequence tid/16, 4 floats at 4*(tid%16))
@@ -148,9 +149,10 @@ lstm_seq_kernel(const __grid_constant__ LstmSeqArgs a) {
     const float ec = ex2_approx(fminf(c * -2.885390081777927f, 40.f));
     const float h = (1.f - ec) * rcp_approx((1.f + eo) * (1.f + ec));
     {
-      const __nv_bfloat16 hh = __float2bfloat16_rn(h);
-      hB[nxt][0][sl][unit] = hh;
-      hB[nxt][1][sl][unit] = __float2bfloat16_rn(h - __bfloat162float(hh));
+      uint16_t hh, hl;
+      split1(h, hh, hl);
+      reinterpret_cast<uint16_t&>(hB[nxt][0][sl][unit]) = hh;
+      reinterpret_cast<uint16_t&>(hB[nxt][1][sl][unit]) = hl;
       hF[nxt][sl][unit] = h;
     }
     if (t == a.nsteps - 1 && valid && a.hN != nullptr) {

@@ -165,12 +165,23 @@ __device__ __forceinline__ float rcp_approx(float x) {
 }
 
 // ---- fp32 -> (hi, lo) bf16 split: x ~= hi + lo with |x - hi - lo| <= 2^-17 |x| -------------------
+// Integer rounding (add half an ulp, keep the upper 16 bits) on the ALU pipe: the cvt.rn.bf16x2.f32
+// form (F2FP) issues on the quarter-rate XU pipe it shares with MUFU, and ncu showed that pipe 92 %
+// busy with conversions alone in the GEMM producers. Ties round away from zero instead of to even;
+// inputs are finite activations/weights.
+__device__ __forceinline__ uint32_t bf16_round_bits(float x) { return __float_as_uint(x) + 0x8000u; }
 __device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
-  const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-  const float2 hf = __bfloat1622float2(h);
-  const __nv_bfloat162 l = __floats2bfloat162_rn(a - hf.x, b - hf.y);
-  hi = *reinterpret_cast<const uint32_t*>(&h);
-  lo = *reinterpret_cast<const uint32_t*>(&l);
+  const uint32_t ra = bf16_round_bits(a), rb = bf16_round_bits(b);
+  hi = __byte_perm(ra, rb, 0x7632);                    // {upper half of rb, upper half of ra}
+  const float la = a - __uint_as_float(ra & 0xffff0000u);
+  const float lb = b - __uint_as_float(rb & 0xffff0000u);
+  lo = __byte_perm(bf16_round_bits(la), bf16_round_bits(lb), 0x7632);
+}
+// single value: the two 16-bit patterns
+__device__ __forceinline__ void split1(float a, uint16_t& hi, uint16_t& lo) {
+  const uint32_t ra = bf16_round_bits(a);
+  hi = (uint16_t)(ra >> 16);
+  lo = (uint16_t)(bf16_round_bits(a - __uint_as_float(ra & 0xffff0000u)) >> 16);
 }
 
 }  // namespace ptx

@@ -9,18 +9,29 @@
 // which reproduces the fp32 path to ~1e-5 end to end at 3 bf16 MMAs per product.
 //
 // Persistent, warp-specialised CTA (one per SM), tiles of 128 rows x up to 256 columns:
-//   warps 0-7  A producers : fp32 global -> registers (one K chunk ahead of the smem stage, so the
-//                            HBM latency overlaps the previous chunk) -> (hi, lo) bf16 -> 128B-swizzled smem
-//   W tiles                : the weights are packed as ready-made swizzled [bn x 64] bf16 blocks
+//   8 warps    A producers : fp32 global (512-byte runs per warp request) -> registers, one K chunk
+//                            ahead of the smem stage -> (hi, lo) bf16 (integer rounding on the ALU pipe,
+//                            ptx.cuh split2) -> 128B-swizzled smem
+//   1 warp     W loader    : the weights are packed as ready-made swizzled [bn x 64] bf16 blocks
 //                            (pack.cu), so one thread fetches a hi and a lo block per K chunk with
 //                            cp.async.bulk (TMA engine, completes on the stage's mbarrier)
-//   warp  8    MMA issuer  : one thread issues tcgen05.mma (M=128, N<=256, K=16) x 12 per 64-wide
+//   1 warp     MMA issuer  : one thread issues tcgen05.mma (M=128, N<=256, K=16) x 12 per 64-wide
 //                            K chunk; tcgen05.commit frees the smem stage / publishes the tile
-//   warps 9-12 epilogue    : tcgen05.ld TMEM -> registers -> per-warp smem transpose, then bias +
+//   4 warps    epilogue    : tcgen05.ld TMEM -> registers -> per-warp smem transpose, then bias +
 //                            LeakyReLU (+residual, *x) on rows of 32 consecutive columns so that every
-//                            global load/store of the epilogue is a full 128-byte line
+//                            global load/store of the epilogue is a full 128-byte line; the residual /
+//                            mask operands of a chunk are all requested before the TMEM read
 // Two smem stages (mbarrier full/empty ring) and two 256-column TMEM accumulators (full/empty
 // barriers) let producer, tensor core and epilogue overlap across K chunks and across tiles.
+//
+// What bounds it (round-1 measurements, tools/mma_bench*.cu, tools/trace_tc.py, profiles/):
+// tcgen05.mma itself runs at 128-142 cycles per M128xN256xK16 instruction in this operand pattern,
+// also under concurrent LDG/STS/bulk-copy traffic, i.e. 1.7k cycles per chunk; the pipeline
+// delivers a chunk every ~5k cycles. Each chunk makes the SM pull 32 KB of A and 64 KB of W
+// through L2 (the weights are re-streamed for every 128-row tile); deeper A prefetch, fully
+// coalesced loads, cheaper conversion and SMSP placement of the roles all left that period
+// unchanged, a TMEM-resident A operand (lstm_tc.cu style) lost more to row-per-thread loads than
+// it saved. The remaining lever is the CTA pair (cta_group::2: half of W per SM) - next round.
 #include "kernels.cuh"
 #include "ptx.cuh"
 
@@ -38,10 +49,21 @@ constexpr int W_PLANE = BN_MAX * 128;        // bytes of one W plane per stage (
 constexpr int STAGE_BYTES = 2 * A_PLANE + 2 * W_PLANE;   // 96 KB
 constexpr int STG_LD = 36;                              // staging row stride (floats): conflict-free 16B access
 constexpr int STG_WARP = 32 * STG_LD * 4;               // bytes of one epilogue warp's 32x32 staging tile
+// Warp roles are placed by scheduler (SMSP = warp % 4). The thread that issues tcgen05.mma occupies its
+// SMSP's dispatch port for the whole MMA batch (pipeline trace: warps sharing that SMSP made no
+// progress while a batch was being issued), so no producer shares the MMA warp's SMSP:
+//   warp 0            MMA issuer (SMSP 0)          warps 4, 8      idle
+//   warps 1-3,5-7,9,10  A producers (SMSPs 1-3)    warp 11         W loader
+//   warps 12-15       epilogue (TMEM lane quarter = warp % 4)
 constexpr int N_A_WARPS = 8, N_EPI_WARPS = 4;
+constexpr int W_WARP = 11, EPI_WARP0 = 12;
+__device__ __forceinline__ int producer_rank(int warp) {      // 1,2,3,5,6,7,9,10 -> 0..7 ; others -1
+  if ((warp & 3) == 0 || warp > 10) return -1;
+  return (warp >> 2) * 3 + (warp & 3) - 1;
+}
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + N_EPI_WARPS * STG_WARP + 1024;  // + alignment slack
-constexpr int MMA_WARP = N_A_WARPS;                      // 8
-constexpr int THREADS = (N_A_WARPS + 1 + N_EPI_WARPS) * 32;   // 416
+constexpr int MMA_WARP = 0;
+constexpr int THREADS = 16 * 32;
 constexpr int N_PRODUCERS = N_A_WARPS * 32;                   // 256
 constexpr int TMEM_COLS = 512;       // 2 accumulators x 256 fp32 columns
 
@@ -74,8 +96,9 @@ __device__ __forceinline__ Tile decode_tile(const TcArgs& args, int tile) {
   const int local = tile - P.tile_start;
   Tile t;
   t.pi = pi;
-  t.m0 = (local % P.tiles_m) * BM;            // m fastest: concurrent CTAs share the W tile in L2
-  t.n0 = (local / P.tiles_m) * BN_MAX;
+  const int tiles_n = (P.N + BN_MAX - 1) / BN_MAX;
+  t.m0 = (local / tiles_n) * BM;              // n fastest: the CTAs of a wave read different W blocks
+  t.n0 = (local % tiles_n) * BN_MAX;
   const int npad = (P.N + 63) & ~63;
   t.bn = min(BN_MAX, npad - t.n0);
   return t;
@@ -85,52 +108,66 @@ __device__ __forceinline__ Tile decode_tile(const TcArgs& args, int tile) {
 __device__ __forceinline__ uint32_t sw128(int r, int c) { return (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4)); }
 
 // ---- A producer: 128 rows x 64 k of fp32 -> hi/lo bf16 planes --------------------------------
-// 256 threads; thread t owns the 8-float groups g = t + 256 i (row g/8, 16-byte chunk g%8), i < 4.
-struct AChunk { float4 v[4][2]; };
+// 256 threads; thread t owns the float4 units u = t + 256 i (row u/16, floats 4(u%16)..+3), i < 8, so
+// every warp-level load covers 512 consecutive bytes (2 rows x 256 B): full sectors per request.
+struct AChunk { float4 v[8]; };
 
 __device__ __forceinline__ void load_a(const TcProb& P, int m0, int k0, int t, AChunk& a) {
   const bool vec = ((P.lda & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.A) & 15) == 0);
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int g = t + 256 * i;
-    const int r = g >> 3, c = g & 7;
-    const int m = m0 + r, k = k0 + c * 8;
-    float4 x0 = make_float4(0.f, 0.f, 0.f, 0.f), x1 = x0;
+  for (int i = 0; i < 8; ++i) {
+    const int u = t + 256 * i;
+    const int r = u >> 4, c = u & 15;
+    const int m = m0 + r, k = k0 + c * 4;
+    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
     if (m < P.M && k < P.K) {
       const float* p = P.A + (long long)m * P.lda + k;
-      if (vec && k + 7 < P.K) {
-        x0 = __ldg(reinterpret_cast<const float4*>(p));
-        x1 = __ldg(reinterpret_cast<const float4*>(p) + 1);
+      if (vec && k + 3 < P.K) {
+        x = __ldg(reinterpret_cast<const float4*>(p));
       } else {
-        float e[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) e[j] = (k + j < P.K) ? __ldg(p + j) : 0.f;
-        x0 = make_float4(e[0], e[1], e[2], e[3]);
-        x1 = make_float4(e[4], e[5], e[6], e[7]);
+        x.x = __ldg(p);
+        if (k + 1 < P.K) x.y = __ldg(p + 1);
+        if (k + 2 < P.K) x.z = __ldg(p + 2);
+        if (k + 3 < P.K) x.w = __ldg(p + 3);
       }
     }
-    a.v[i][0] = x0;
-    a.v[i][1] = x1;
+    a.v[i] = x;
   }
 }
 
 __device__ __forceinline__ void store_a(const AChunk& a, uint8_t* a_hi, uint8_t* a_lo, int t) {
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int g = t + 256 * i;
-    const int r = g >> 3, c = g & 7;
-    uint4 h, l;
-    split2(a.v[i][0].x, a.v[i][0].y, h.x, l.x);
-    split2(a.v[i][0].z, a.v[i][0].w, h.y, l.y);
-    split2(a.v[i][1].x, a.v[i][1].y, h.z, l.z);
-    split2(a.v[i][1].z, a.v[i][1].w, h.w, l.w);
-    const uint32_t off = sw128(r, c);
-    *reinterpret_cast<uint4*>(a_hi + off) = h;
-    *reinterpret_cast<uint4*>(a_lo + off) = l;
+  for (int i = 0; i < 8; ++i) {
+    const int u = t + 256 * i;
+    const int r = u >> 4, c = u & 15;
+    uint2 h, l;
+    split2(a.v[i].x, a.v[i].y, h.x, l.x);
+    split2(a.v[i].z, a.v[i].w, h.y, l.y);
+    const uint32_t off = sw128(r, c >> 1) + (c & 1) * 8;     // half of a 16-byte swizzle chunk
+    *reinterpret_cast<uint2*>(a_hi + off) = h;
+    *reinterpret_cast<uint2*>(a_lo + off) = l;
   }
 }
 
 __device__ __forceinline__ float lrelu(float v) { return v > 0.f ? v : v * 0.01f; }
+
+#ifdef BSB_TRACE
+// pipeline timeline of CTA 0 (debug builds only): three role regions of 3000 (code, clock) pairs,
+// a private counter per role (no atomics: tracing must not stretch the pipeline it observes)
+__device__ unsigned long long* g_trace = nullptr;
+#define TRACE_DECL int trace_n = 0
+#define TRACE(role, code)                                                            \
+  do {                                                                               \
+    if (blockIdx.x == 0 && g_trace != nullptr && trace_n < 3000) {                   \
+      g_trace[(role) * 6000 + 2 * trace_n] = (unsigned long long)(code);             \
+      g_trace[(role) * 6000 + 2 * trace_n + 1] = (unsigned long long)clock64();      \
+      ++trace_n;                                                                     \
+    }                                                                                \
+  } while (0)
+#else
+#define TRACE_DECL
+#define TRACE(role, code)
+#endif
 
 __global__ void __launch_bounds__(THREADS, 1)
 tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
@@ -163,9 +200,16 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
+  TRACE_DECL;
 
-  if (warp < MMA_WARP) {
-    // ================= producers =================
+  const int prank = producer_rank(warp);
+  if (prank >= 0) {
+    // ================= A producers =================
+    const int pt = prank * 32 + lane;           // producer thread 0..255
+    // One K chunk of A is prefetched into registers while the previous one is converted and stored.
+    // (Two chunks in flight were measured and did not help: at this tile shape the kernel is bound by
+    // the bytes each SM must pull from L2 - 32 KB of A plus 64 KB of W per 128x256x64 chunk - not by
+    // the latency of any one of them; see DESIGN.md.)
     int stage = 0;
     uint32_t phase = 0;
     int tile = blockIdx.x, kc = 0, nk = 0;
@@ -174,26 +218,18 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
     if (tile < args.total_tiles) {
       T = decode_tile(args, tile);
       nk = (args.p[T.pi].K + BK - 1) / BK;
-      load_a(args.p[T.pi], T.m0, 0, tid, regs);
+      load_a(args.p[T.pi], T.m0, 0, pt, regs);
     }
     while (tile < args.total_tiles) {
-      const TcProb& P = args.p[T.pi];
       mbar_wait(smem_u32(&bar_empty[stage]), phase ^ 1);
+      if (pt == 0) TRACE(0, 1);
       uint8_t* sb = smem_gen + stage * STAGE_BYTES;
-      if (tid == 0) {
-        // W blocks [bn x 64] bf16, already swizzled: (n0 * nch + kc * bn) * 128 bytes into each plane
-        const uint32_t bytes = (uint32_t)T.bn * 128u;
-        const long long off = ((long long)T.n0 * (P.ldw >> 6) + (long long)kc * T.bn) * 128;
-        const uint32_t bar = smem_u32(&bar_full[stage]);
-        mbar_arrive_expect_tx(bar, 2 * bytes);
-        bulk_g2s(smem_base + stage * STAGE_BYTES + 2 * A_PLANE, reinterpret_cast<const uint8_t*>(P.Wh) + off, bytes, bar);
-        bulk_g2s(smem_base + stage * STAGE_BYTES + 2 * A_PLANE + W_PLANE, reinterpret_cast<const uint8_t*>(P.Wl) + off, bytes, bar);
-      }
-      store_a(regs, sb, sb + A_PLANE, tid);
+      store_a(regs, sb, sb + A_PLANE, pt);
+      if (pt == 0) TRACE(0, 2);
       fence_proxy_async_smem();
       mbar_arrive(smem_u32(&bar_full[stage]));
+      if (pt == 0) TRACE(0, 3);
       if (++stage == STAGES) { stage = 0; phase ^= 1; }
-      // next chunk: its global loads fly while the tensor core works on the stage just filled
       if (++kc == nk) {
         kc = 0;
         tile += gridDim.x;
@@ -202,7 +238,30 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
           nk = (args.p[T.pi].K + BK - 1) / BK;
         }
       }
-      if (tile < args.total_tiles) load_a(args.p[T.pi], T.m0, kc * BK, tid, regs);
+      if (tile < args.total_tiles) load_a(args.p[T.pi], T.m0, kc * BK, pt, regs);
+      if (pt == 0) TRACE(0, 4);
+    }
+  } else if (warp == W_WARP) {
+    // ================= W loader (one thread) =================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
+        const Tile T = decode_tile(args, tile);
+        const TcProb& P = args.p[T.pi];
+        const int nk = (P.K + BK - 1) / BK;
+        for (int kc = 0; kc < nk; ++kc) {
+          mbar_wait(smem_u32(&bar_empty[stage]), phase ^ 1);
+          // W blocks [bn x 64] bf16, already swizzled: (n0 * nch + kc * bn) * 128 bytes into each plane
+          const uint32_t bytes = (uint32_t)T.bn * 128u;
+          const long long off = ((long long)T.n0 * (P.ldw >> 6) + (long long)kc * T.bn) * 128;
+          const uint32_t bar = smem_u32(&bar_full[stage]);
+          mbar_arrive_expect_tx(bar, 2 * bytes);
+          bulk_g2s(smem_base + stage * STAGE_BYTES + 2 * A_PLANE, reinterpret_cast<const uint8_t*>(P.Wh) + off, bytes, bar);
+          bulk_g2s(smem_base + stage * STAGE_BYTES + 2 * A_PLANE + W_PLANE, reinterpret_cast<const uint8_t*>(P.Wl) + off, bytes, bar);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
     }
   } else if (warp == MMA_WARP) {
     // ================= MMA issuer =================
@@ -213,11 +272,13 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
       const TcProb& P = args.p[T.pi];
       const int nk = (P.K + BK - 1) / BK;
       mbar_wait(smem_u32(&bar_tempty[acc]), acc_phase ^ 1);   // epilogue has drained this accumulator
+      if (lane == 0) TRACE(1, 10);
       tc_fence_after();
       const uint32_t idesc = make_idesc_bf16(BM, T.bn);
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN_MAX);
       for (int kc = 0; kc < nk; ++kc) {
         mbar_wait(smem_u32(&bar_full[stage]), phase);
+        if (lane == 0) TRACE(1, 11);
         tc_fence_after();
         if (lane == 0) {
           const uint32_t sb = smem_base + stage * STAGE_BYTES;
@@ -234,16 +295,17 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
           }
           mma_commit(smem_u32(&bar_empty[stage]));             // smem stage reusable once these MMAs retire
           if (kc == nk - 1) mma_commit(smem_u32(&bar_tfull[acc]));
+          TRACE(1, 12);
         }
         __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
-  } else {
+  } else if (warp >= EPI_WARP0) {
     // ================= epilogue =================
     const int q = warp & 3;                 // TMEM lane quarter this warp may access
-    float* stg = reinterpret_cast<float*>(smem_gen + STAGES * STAGE_BYTES + (warp - MMA_WARP - 1) * STG_WARP);
+    float* stg = reinterpret_cast<float*>(smem_gen + STAGES * STAGE_BYTES + (warp - EPI_WARP0) * STG_WARP);
     const int cg = lane & 7, sub = lane >> 3;   // transposed phase: 4 columns at 4*cg of rows sub + 4k
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -251,6 +313,7 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
       const Tile T = decode_tile(args, tile);
       const TcProb& P = args.p[T.pi];
       mbar_wait(smem_u32(&bar_tfull[acc]), acc_phase);
+      if (warp == EPI_WARP0 && lane == 0) TRACE(2, 20);
       tc_fence_after();
       const int mw = T.m0 + q * 32;           // first row of this warp
       const bool o_vec = ((P.ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.O) & 15) == 0);
@@ -334,6 +397,7 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
       }
       tc_fence_before();
       mbar_arrive(smem_u32(&bar_tempty[acc]));
+      if (warp == EPI_WARP0 && lane == 0) TRACE(2, 21);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   }
@@ -396,5 +460,11 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
   count_launch();
   return cudaGetLastError();
 }
+
+#ifdef BSB_TRACE
+extern "C" int bsb_debug_set_trace(void* p) {
+  return (int)cudaMemcpyToSymbol(g_trace, &p, sizeof(p));
+}
+#endif
 
 }  // namespace bsb

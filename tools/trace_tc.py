@@ -1,0 +1,40 @@
+"""Debug: pipeline timeline of CTA 0 of the tensor-core Linear kernel (needs a -DBSB_TRACE build)."""
+import ctypes, sys, os, io, contextlib
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from speechseparation_b200 import BSRNN, _lib
+torch.set_grad_enabled(False)
+l = _lib.lib()
+l.bsb_debug_set_trace.argtypes = [ctypes.c_void_p]
+with contextlib.redirect_stdout(io.StringIO()):
+    m = BSRNN().cuda().eval()
+C, T = 64, 431
+R = C * T
+packed = m.packed_weights(torch.device("cuda", 0))
+ws = torch.empty(l.bsb_workspace_bytes(C, T), dtype=torch.uint8, device="cuda")
+xf = torch.randn(R, 2052, device="cuda")
+residual = torch.zeros(R, 2052, device="cuda")
+feat = torch.zeros(R, 12, 64, device="cuda")
+s = torch.cuda.current_stream().cuda_stream
+for _ in range(2):
+    _lib.check(l.bsb_bandsplit(xf.data_ptr(), R, packed.data_ptr(), residual.data_ptr(), feat.data_ptr(), ws.data_ptr(), ws.numel(), s))
+torch.cuda.synchronize()
+tr = torch.zeros(3 * 6000, dtype=torch.int64, device="cuda")
+l.bsb_debug_set_trace(tr.data_ptr())
+_lib.check(l.bsb_bandsplit(xf.data_ptr(), R, packed.data_ptr(), residual.data_ptr(), feat.data_ptr(), ws.data_ptr(), ws.numel(), s))
+torch.cuda.synchronize()
+l.bsb_debug_set_trace(None)
+t = tr.cpu().tolist()
+ev = []
+for role in range(3):
+    for i in range(3000):
+        code, clk = t[role * 6000 + 2 * i], t[role * 6000 + 2 * i + 1]
+        if code: ev.append((clk, code))
+ev.sort()
+n = len(ev)
+t0 = ev[0][0]
+names = {1: "P empty-acq", 2: "P A-stored", 3: "P arrived", 4: "P loads-issued", 10: "M tempty-acq", 11: "M full-acq", 12: "M issued", 20: "E tfull-acq", 21: "E done"}
+with open("gpurun_out/trace_tc.txt", "w") as f:
+    for c, code in ev[:1500]:
+        f.write(f"{c - t0:9d} {names.get(code, code)}\n")
+print("events", n)
