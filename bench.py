@@ -49,8 +49,21 @@ def synth(rows: int, n: int, device, seed: int = 1234) -> torch.Tensor:
     return out.to(device)
 
 
+# which kernel runs each timed stage, and how many launches of it the stage holds
+GEMM = "tc_grouped_linear_kernel"
+STAGE_KERNEL = {"stft": ("stft_warp_kernel", 1), "istft": ("istft_warp_kernel", 1), "pre": (GEMM, 2), "bandfc": (GEMM, 3),
+                "back": (GEMM, 3), "post_mask": (GEMM, 2)}
+for _j in range(4):
+    _k = "lstm_tc_kernel" if _j % 2 == 0 else "lstm_seq_kernel"
+    STAGE_KERNEL[f"rnn{_j}.rec0"] = (_k, 1)
+    STAGE_KERNEL[f"rnn{_j}.rec1"] = (_k, 1)
+    STAGE_KERNEL[f"rnn{_j}.fc"] = (GEMM, 1)
+
+
 def stage_work(T: int):
-    """Algorithmic FLOPs and bytes per frame-row of each timed stage; fp32."""
+    """Algorithmic FLOPs (2 x the reference's MACs, fp32) and HBM bytes per frame-row of each timed
+    stage. The LSTM stages include fc_in and the W_ih projections,
+    which are fused into the recurrence kernels; their bytes are input read once + output written."""
     mac = {}
     mac["pre"] = sum(2 * d * d for d in BAND_D)
     mac["bandfc"] = sum(d * max(d, 64) + max(d, 64) * 64 + 64 * 64 for d in BAND_D)
@@ -58,10 +71,8 @@ def stage_work(T: int):
     mac["post_mask"] = sum(2 * d * d for d in BAND_D)
     for j in range(4):
         nd = 2 if j % 2 == 0 else 1
-        mac[f"rnn{j}.proj0"] = 12 * (64 * 64 + 64 * 256 * nd)
-        mac[f"rnn{j}.proj1"] = 12 * (64 * nd * 256 * nd)
-        mac[f"rnn{j}.rec0"] = 12 * (64 * 256 * nd)
-        mac[f"rnn{j}.rec1"] = 12 * (64 * 256 * nd)
+        mac[f"rnn{j}.rec0"] = 12 * (64 * 64 + 64 * 256 * nd + 64 * 256 * nd)
+        mac[f"rnn{j}.rec1"] = 12 * (64 * nd * 256 * nd + 64 * 256 * nd)
         mac[f"rnn{j}.fc"] = 12 * (64 * nd * 64)
     flops = {k: 2.0 * v for k, v in mac.items()}
     flops["stft"] = flops["istft"] = 5.0 * 1024 * 10 + 8 * 1024      # 1024-pt complex FFT + split
@@ -69,9 +80,8 @@ def stage_work(T: int):
            "back": 3072 + 8200, "post_mask": 8200 * 4}
     for j in range(4):
         nd = 2 if j % 2 == 0 else 1
-        byt[f"rnn{j}.proj0"] = 3072 + 12 * 256 * nd * 4
-        byt[f"rnn{j}.proj1"] = 12 * 64 * nd * 4 + 12 * 256 * nd * 4
-        byt[f"rnn{j}.rec0"] = byt[f"rnn{j}.rec1"] = 12 * 256 * nd * 4 + 12 * 64 * nd * 4
+        byt[f"rnn{j}.rec0"] = 3072 + 12 * 64 * nd * 4
+        byt[f"rnn{j}.rec1"] = 12 * 64 * nd * 4 * 2
         byt[f"rnn{j}.fc"] = 12 * 64 * nd * 4 + 3072 * 2
     return flops, byt
 
@@ -158,6 +168,40 @@ def cpu_baseline(rows: int, n: int, repeats: int = 3):
             "sample": f"{rows} x {n / SR:.1f} s clips, best of {repeats}, oracle/bsrnn_oracle.py (torch {torch.__version__} CPU fp32)"}
 
 
+def streaming_latency(model, dev, hops: int = 400, rows: int = 2):
+    """BASELINE.json configs[2]: batch 1 (2 stereo rows), hop by hop with carried LSTM state
+    (infer-streaming.py:104-147). `device_ms`: CUDA events around one hop with the 1024 new samples
+    already in device memory; `host_ms`: wall clock of H2D copy from pinned memory + hop + D2H copy +
+    synchronize, i.e. what the audio thread of a plugin would wait for. Hop budget: 1024/44100 s."""
+    from speechseparation_b200 import StreamingSeparator
+    sep = StreamingSeparator(model, rows=rows)
+    g = torch.Generator().manual_seed(7)
+    chunks = (0.1 * torch.randn(hops + 8, rows, 1024, generator=g)).pin_memory()
+    out_h = torch.empty(rows, 1024).pin_memory()
+    dchunk = torch.empty(rows, 1024, device=dev)
+    for i in range(8):                                   # warm-up: first hops + graph capture
+        sep.step(chunks[i])
+    torch.cuda.synchronize()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(hops)]
+    host = []
+    for i in range(hops):
+        t0 = time.perf_counter()
+        dchunk.copy_(chunks[8 + i], non_blocking=True)
+        ev[i][0].record()
+        out = sep.step(dchunk)
+        ev[i][1].record()
+        out_h.copy_(out, non_blocking=True)
+        torch.cuda.synchronize()
+        host.append(1e3 * (time.perf_counter() - t0))
+    devms = sorted(a.elapsed_time(b) for a, b in ev)
+    host.sort()
+    q = lambda v, p: v[min(len(v) - 1, int(p * len(v)))]
+    return {"config": f"{rows} rows x 1024-sample hops, CUDA graph per hop, {hops} hops",
+            "device_ms_p50": q(devms, 0.5), "device_ms_p99": q(devms, 0.99),
+            "host_ms_p50": q(host, 0.5), "host_ms_p99": q(host, 0.99),
+            "hop_budget_ms": 1e3 * 1024 / SR, "realtime_factor_p99": (1e3 * 1024 / SR) / q(host, 0.99)}
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference's own CPU implementation of the path (stock PyTorch ops,
     restated in oracle/) on all host cores; each step is a bounded sample of the workload."""
@@ -197,6 +241,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="cfg2_offline_64x10s", choices=list(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-streaming", action="store_true", help="skip the cfg-3 per-hop latency measurement")
+    ap.add_argument("--stream-hops", type=int, default=400)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -278,23 +324,58 @@ def main():
         if world > 1:
             dist.destroy_process_group()
         return
-    # ---- roofline of the dominant stage ----------------------------------------------------------
+    # ---- per-kernel accounting and the roofline of the dominant kernel -------------------------------
     pk = peaks()
     flops, byt = stage_work(T)
-    top = max(stage_ms, key=stage_ms.get)
     total_ms = sum(stage_ms.values())
-    t_top = stage_ms[top] / 1e3
-    hbm_ach = byt[top] * frame_rows / t_top / 1e9
-    fl_ach = flops[top] * frame_rows / t_top / 1e12
-    # a stage is HBM-bound if its HBM time at peak exceeds its tensor time at peak
-    hbm_bound = (byt[top] / pk["hbm"] / 1e9) > (flops[top] / pk["tensor"] / 1e12)
-    roof = ({"bound": "hbm", "achieved": hbm_ach, "peak": pk["hbm"], "unit": "GB/s", "frac": hbm_ach / pk["hbm"]}
-            if hbm_bound else
-            {"bound": "tensor", "achieved": fl_ach, "peak": pk["tensor"], "unit": "TFLOP/s", "frac": fl_ach / pk["tensor"]})
-    roof.update({"kernel": top, "share_of_step": stage_ms[top] / total_ms, "traffic": None,
-                 "peak_source": pk["src"], "arith": "fp32 FFMA (no tensor cores yet)"})
+    kern = {}
+    for st_name, ms in stage_ms.items():
+        kname, nl = STAGE_KERNEL[st_name]
+        k = kern.setdefault(kname, {"ms": 0.0, "launches": 0, "flops": 0.0, "bytes": 0.0})
+        k["ms"] += ms
+        k["launches"] += nl
+        k["flops"] += flops[st_name] * frame_rows
+        k["bytes"] += byt[st_name] * frame_rows
+    for k in kern.values():
+        k["tflops"] = k["flops"] / (k["ms"] / 1e3) / 1e12
+        k["gbs"] = k["bytes"] / (k["ms"] / 1e3) / 1e9
+        k["hbm_frac"] = k["gbs"] / pk["hbm"]
+        k["share_of_step"] = k["ms"] / total_ms
+        k["avg_launch_ms"] = k["ms"] / k["launches"]
+    top = max(kern, key=lambda n_: kern[n_]["ms"])
+    K = kern[top]
+    # a kernel is HBM-bound if its HBM time at peak exceeds its tensor time at peak
+    tpeak = pk["tensor_sustained"] or pk["tensor"]        # timed inside a long step: the sustained figure
+    # (the tensor pipe executes 3 bf16 MMAs per algorithmic fp32 product in the split-bf16 GEMM)
+    tensor_ops = 3.0 if top == GEMM else 1.0
+    hbm_bound = (K["bytes"] / pk["hbm"] / 1e9) > (tensor_ops * K["flops"] / tpeak / 1e12)
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if os.path.exists(tp):
+        traffic = json.load(open(tp)).get(top)
+    if hbm_bound:
+        roof = {"bound": "hbm", "achieved": K["gbs"], "peak": pk["hbm"], "unit": "GB/s", "frac": K["hbm_frac"]}
+    else:
+        roof = {"bound": "tensor", "achieved": K["tflops"], "peak": tpeak, "unit": "TFLOP/s", "frac": K["tflops"] / tpeak,
+                "tensor_ops_per_flop": 3, "tensor_pipe_frac": 3.0 * K["tflops"] / tpeak,
+                "arith": "split-bf16: 3 bf16 tcgen05.mma per fp32 product (A_hi.W_hi + A_hi.W_lo + A_lo.W_hi), fp32 accumulate "
+                         "in TMEM; `achieved` counts the algorithmic fp32 FLOPs once, the tensor pipe executes 3x that"}
+    roof.update({"kernel": top, "launches_per_step": K["launches"], "avg_launch_ms": K["avg_launch_ms"],
+                 "algorithmic_flops_per_launch": K["flops"] / K["launches"],
+                 "algorithmic_bytes_per_launch": K["bytes"] / K["launches"],
+                 "share_of_step": K["share_of_step"], "traffic": traffic, "peak_source": pk["src"] + " (sustained bf16)"})
     stages = {k: {"ms": v, "tflops": flops[k] * frame_rows / (v / 1e3) / 1e12,
                   "gbs": byt[k] * frame_rows / (v / 1e3) / 1e9} for k, v in stage_ms.items()}
+    kernels = {n_: {"ms": round(v["ms"], 4), "launches": v["launches"], "tflops": round(v["tflops"], 2),
+                    "gbs": round(v["gbs"], 1), "hbm_frac": round(v["hbm_frac"], 3), "share_of_step": round(v["share_of_step"], 3)}
+               for n_, v in kern.items()}
+    # serial depth of the time-axis recurrence: device time of one layer / its T steps
+    rec_us = None
+    if "rnn1.rec0" in stage_ms:
+        rec_us = {"time_axis_us_per_step": 1e3 * stage_ms["rnn1.rec0"] / T,
+                  "band_axis_us_per_step_per_tile": 1e3 * stage_ms["rnn0.rec0"] / 12 / max(1, -(-(2 * -(-frame_rows // 128)) // 148)),
+                  "note": "time axis: one lstm_seq_kernel layer / T steps (8 sequences per CTA); band axis: one lstm_tc_kernel "
+                          "layer / 12 steps / waves of 128-sequence tiles over 148 SMs"}
     res = {
         "metric": "audio-sec separated/sec", "value": units / tmax, "unit": "audio-sec/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tmax / args.steps,
@@ -304,8 +385,11 @@ def main():
                    "weights": "random init, torch.manual_seed(0)"},
         "e2e": {"value": units_e / tmax_e, "unit": "audio-sec/s", "h2d_bytes_per_step": host_in.numel() * 4,
                 "d2h_bytes_per_step": host_out.numel() * 4},
-        "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "stages": stages,
+        "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "kernels": kernels,
+        "recurrence_latency": rec_us, "stages": stages,
     }
+    if world == 1 and not args.no_streaming:
+        res["streaming"] = streaming_latency(model, dev, hops=args.stream_hops)
     if world == 1 and not args.no_cpu_baseline:
         res["cpu_baseline"] = cpu_baseline(min(rows, 4), n)
     print(json.dumps(res))
