@@ -158,3 +158,87 @@ class StreamingSeparator:
                 self._enqueue(parity)
             self.hops += 1
         return self.out
+
+
+class BatchSeparator:
+    """Host-buffer front end of ``BSRNN.separate`` for bulk offline separation (the loop of
+    gendataset-separate.py / infer.py over many clips): batches of [rows, L] arrive in pinned host
+    memory and leave as [rows, 1024*(T-1)] in pinned host memory.
+
+    The three legs of a batch -- host->device copy, the separation kernels, device->host copy -- run on
+    three streams over ``depth`` device buffer pairs, so the copies of neighbouring batches overlap the
+    kernels (PCIe is full duplex). Results are identical to calling ``model.separate`` per batch: the
+    kernels of consecutive batches still run one after the other on one stream and share one workspace.
+    """
+
+    class Ticket:
+        def __init__(self, event, out):
+            self.event, self.out = event, out
+
+        def wait(self) -> torch.Tensor:
+            self.event.synchronize()
+            return self.out
+
+    def __init__(self, model: BSRNN, rows: int, samples: int, device=None, depth: int = 2,
+                 window: Optional[torch.Tensor] = None):
+        dev = torch.device(device) if device is not None else next(model.parameters()).device
+        if dev.type != "cuda":
+            raise RuntimeError("BatchSeparator needs a CUDA device: speechseparation_b200 has no CPU path")
+        T = _lib.lib().bsb_num_frames(samples)
+        if T < 2 or rows < 1 or depth < 1:
+            raise RuntimeError(f"bad batch shape rows={rows} samples={samples} depth={depth}")
+        _check_window(window, dev)
+        self.model, self.dev, self.rows, self.samples, self.depth, self.window = model, dev, rows, samples, depth, window
+        self.out_samples = HOP * (T - 1)
+        with torch.cuda.device(dev):
+            self.s_in, self.s_run, self.s_out = (torch.cuda.Stream(dev) for _ in range(3))
+            self.d_in = [torch.empty(rows, samples, device=dev) for _ in range(depth)]
+            self.d_out = [torch.empty(rows, self.out_samples, device=dev) for _ in range(depth)]
+            self.ev_in = [torch.cuda.Event() for _ in range(depth)]
+            self.ev_run = [torch.cuda.Event() for _ in range(depth)]
+            self.ev_out = [torch.cuda.Event() for _ in range(depth)]
+        self.used = [False] * depth
+        self.n = 0
+
+    def _check_host(self, t: torch.Tensor, shape, what: str):
+        if t.device.type != "cpu" or t.dtype != torch.float32 or tuple(t.shape) != tuple(shape) or not t.is_contiguous():
+            raise RuntimeError(f"{what} must be a contiguous float32 host tensor of shape {tuple(shape)}")
+        if not t.is_pinned():
+            raise RuntimeError(f"{what} must be in pinned host memory (torch.empty(..., pin_memory=True))")
+
+    def after(self, event: torch.cuda.Event):
+        """Order all three legs after ``event`` (e.g. a timing event of the caller's stream)."""
+        for s in (self.s_in, self.s_run, self.s_out):
+            s.wait_event(event)
+
+    def submit(self, host_in: torch.Tensor, host_out: torch.Tensor) -> "BatchSeparator.Ticket":
+        """Enqueue one batch; returns at once. ``host_out`` is valid after ``ticket.wait()``."""
+        self._check_host(host_in, (self.rows, self.samples), "host_in")
+        self._check_host(host_out, (self.rows, self.out_samples), "host_out")
+        b = self.n % self.depth
+        self.n += 1
+        with torch.cuda.device(self.dev):
+            if self.used[b]:
+                self.s_in.wait_event(self.ev_run[b])          # d_in[b] is free once its kernels are done
+            with torch.cuda.stream(self.s_in):
+                self.d_in[b].copy_(host_in, non_blocking=True)
+                self.ev_in[b].record()
+            self.s_run.wait_event(self.ev_in[b])
+            if self.used[b]:
+                self.s_run.wait_event(self.ev_out[b])         # d_out[b] is free once it reached the host
+            with torch.cuda.stream(self.s_run):
+                self.model.separate(self.d_in[b], self.window, out=self.d_out[b])
+                self.ev_run[b].record()
+            self.s_out.wait_event(self.ev_run[b])
+            with torch.cuda.stream(self.s_out):
+                host_out.copy_(self.d_out[b], non_blocking=True)
+                self.ev_out[b].record()
+        self.used[b] = True
+        return BatchSeparator.Ticket(self.ev_out[b], host_out)
+
+    def join(self, stream: Optional[torch.cuda.Stream] = None):
+        """Make ``stream`` (default: the current one) wait for everything submitted so far."""
+        stream = stream if stream is not None else torch.cuda.current_stream(self.dev)
+        for b in range(self.depth):
+            if self.used[b]:
+                stream.wait_event(self.ev_out[b])

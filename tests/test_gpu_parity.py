@@ -281,3 +281,104 @@ def test_tensor_core_linears_match_fp32_kernels(dev, model, oracle_sd):
         st = O.forward_stages(oracle_sd, x)
         assert rel(outs[0][0].reshape(C, T, 2050), st["residual"]) < 5e-5
         assert rel(outs[0][1].reshape(C, T, 12, 64), st["feat"]) < 5e-5
+
+
+def _run_block(l, j, fin, C, T, packed, ws, state_in=None, state_out=None):
+    from speechseparation_b200 import _lib
+    fout = torch.zeros_like(fin)
+    _lib.check(l.bsb_rnn_block(j, fin.data_ptr(), C, T, packed.data_ptr(),
+                               None if state_in is None else state_in.data_ptr(),
+                               None if state_out is None else state_out.data_ptr(),
+                               fout.data_ptr(), ws.data_ptr(), ws.numel(), _s()), f"rnn{j}")
+    torch.cuda.synchronize()
+    return fout
+
+
+@pytest.mark.parametrize("C,T", [(1, 128), (3, 131), (2, 300), (7, 64)])
+def test_band_axis_tensor_core_lstm_vs_oracle(dev, model, oracle_sd, C, T):
+    """BandwiseLSTM blocks (bsrnn.py:138-153) on the tcgen05 kernel (C*T >= 128 sequences; ragged last
+    tile at 393 and 448+... rows) against the ATen LSTM of the oracle and the fp32 FFMA kernels."""
+    from speechseparation_b200 import _lib
+    l = _lib.lib()
+    packed = model.packed_weights(dev)
+    ws = _ws(l, C, T, dev)
+    rs = np.random.RandomState(7 * C + T)
+    fin = torch.from_numpy(rs.standard_normal((C * T, 12, 64)).astype(np.float32))
+    for j in (0, 2):
+        ref, _ = O.rnn_block(oracle_sd, j, fin)
+        got = _run_block(l, j, fin.to(dev), C, T, packed, ws)
+        assert rel(got, ref) < 5e-5, (j, C, T)
+        l.bsb_set_force_fp32(1)
+        try:
+            fp32 = _run_block(l, j, fin.to(dev), C, T, packed, ws)
+        finally:
+            l.bsb_set_force_fp32(0)
+        assert rel(got, fp32) < 5e-5, (j, C, T)
+        assert not torch.equal(got, fp32)          # really a different kernel
+
+
+@pytest.mark.parametrize("C,T,with_state", [(1, 2, False), (1, 3, True), (2, 37, True), (3, 130, False), (5, 64, True)])
+def test_time_axis_lstm_vs_oracle_with_state(dev, model, oracle_sd, C, T, with_state):
+    """TimewiseLSTM blocks (bsrnn.py:101-128) on the 8-sequences-per-CTA kernel: ragged last CTA
+    (12, 24, 36, 60 sequences), initial (h, c) in, final (h, c) out, against the ATen LSTM."""
+    from speechseparation_b200 import _lib
+    l = _lib.lib()
+    packed = model.packed_weights(dev)
+    ws = _ws(l, C, T, dev)
+    rs = np.random.RandomState(11 * C + T)
+    fin = torch.from_numpy(rs.standard_normal((C, T, 12, 64)).astype(np.float32))
+    seqs = fin.permute(0, 2, 1, 3).reshape(C * 12, T, 64)               # the reference's view (bsrnn.py:112-114)
+    for j in (1, 3):
+        st = None
+        if with_state:
+            st = torch.from_numpy((0.5 * rs.standard_normal((2, 2, C * 12, 64))).astype(np.float32))
+        ref, (hn, cn) = O.rnn_block(oracle_sd, j, seqs, None if st is None else (st[0], st[1]))
+        ref = ref.reshape(C, 12, T, 64).permute(0, 2, 1, 3)
+        so = torch.zeros(2, 2, C * 12, 64, device=dev)
+        got = _run_block(l, j, fin.reshape(C * T, 12, 64).to(dev), C, T, packed, ws,
+                         None if st is None else st.to(dev), so)
+        assert rel(got.reshape(C, T, 12, 64), ref) < 5e-5, (j, C, T)
+        assert float((so[0].cpu() - hn).abs().max()) < 2e-5 and float((so[1].cpu() - cn).abs().max()) < 5e-5
+
+
+def test_lstm_saturated_gates_stay_finite(dev, model):
+    """Large activations drive every gate into saturation: the ex2/rcp cell must clamp, not overflow."""
+    from speechseparation_b200 import _lib
+    l = _lib.lib()
+    packed = model.packed_weights(dev)
+    C, T = 2, 130
+    ws = _ws(l, C, T, dev)
+    fin = (torch.randn(C * T, 12, 64, device=dev) * 1e4)
+    for j in range(4):
+        out = _run_block(l, j, fin, C, T, packed, ws)
+        assert bool(torch.isfinite(out).all()), j
+        assert float((out - fin).abs().max()) < 1e3          # |fc(h)| is bounded since |h| <= 1
+
+
+def test_full_size_properties_cfg2_slice(dev, model):
+    """Size-independent properties at a bench-like shape (16 rows x 10 s): row independence across CTA
+    tiles, zero in -> zero out, and silence padding does not leak backwards past the LSTM's reach."""
+    C, L = 16, 441000
+    wav = torch.randn(C, L, device=dev) * 0.1
+    out = model.separate(wav)
+    assert out.shape == (C, 1024 * (L // 1024)) and bool(torch.isfinite(out).all())
+    sub = model.separate(wav[5:7].contiguous())
+    assert rel(sub, out[5:7]) < 1e-5                           # other rows share tiles but not results
+    assert float(model.separate(torch.zeros(2, L, device=dev)).abs().max()) == 0.0
+
+
+def test_batch_separator_pipeline_equals_separate(dev, model):
+    """Host-buffer pipeline (H2D | kernels | D2H on three streams): every batch equals model.separate."""
+    from speechseparation_b200 import BatchSeparator
+    C, L = 3, 20000
+    pipe = BatchSeparator(model, C, L, device=dev)
+    ins = [torch.randn(C, L).mul_(0.1).pin_memory() for _ in range(5)]
+    outs = [torch.empty(C, pipe.out_samples).pin_memory() for _ in range(5)]
+    tickets = [pipe.submit(a, b) for a, b in zip(ins, outs)]
+    for a, t in zip(ins, tickets):
+        got = t.wait()
+        assert torch.equal(got, model.separate(a.to(dev)).cpu())
+    with pytest.raises(RuntimeError):
+        pipe.submit(torch.randn(C, L), outs[0])              # not pinned
+    with pytest.raises(RuntimeError):
+        pipe.submit(ins[0][:, :-1].contiguous().pin_memory(), outs[0])
