@@ -60,7 +60,13 @@ struct Ws {
   float* hbuf;      // [R*12][128]
   float* xf;        // [R][kXS]   (only carved when with_io)
   float* yf;        // [R][kXS]
+  char* planeA;     // two buffers of bf16 hi/lo planes for Linear -> Linear activations (kernels.cuh LinProb::Ap)
+  char* planeB;
+  long long plane_lo;   // byte distance hi -> lo plane inside a buffer
+  long long mtiles;     // 128-row tiles
 };
+// widest layer output in 64-column chunks summed over the 11 bands (bandFCs_back.2: 7 x 2 + 3 + 6 + 12 + 9 = 44)
+constexpr int kPlaneChunksMax = 44;
 
 inline size_t rup256(size_t v) { return (v + 255) / 256 * 256; }
 
@@ -82,6 +88,13 @@ size_t carve(Ws* w, char* base, long long R, bool with_io) {
   p = take((size_t)R * kBands * kFeat); if (w) w->t64 = p;
   p = take((size_t)R * kBands * 2 * kGates); if (w) w->xproj = p;
   p = take((size_t)R * kBands * 2 * kFeat); if (w) w->hbuf = p;
+  {
+    const long long mt = (R + 127) / 128;
+    const size_t plane_floats = (size_t)mt * kPlaneChunksMax * kPlaneBlock / sizeof(float);
+    p = take(2 * plane_floats); if (w) w->planeA = reinterpret_cast<char*>(p);
+    p = take(2 * plane_floats); if (w) w->planeB = reinterpret_cast<char*>(p);
+    if (w) { w->plane_lo = (long long)plane_floats * sizeof(float); w->mtiles = mt; }
+  }
   if (with_io) {
     p = take((size_t)R * kXS); if (w) w->xf = p;
     p = take((size_t)R * kXS); if (w) w->yf = p;
@@ -115,7 +128,32 @@ void set_prob(LinProb& P, const void* packed, const Lin& l, const float* A, int 
   P.M = M; P.N = l.N; P.K = l.K;
   P.act = act;
   P.tile_start = 0; P.tiles_n = 0;
+  P.Ap = nullptr; P.Op = nullptr; P.a_lo = P.o_lo = 0;
 }
+
+// Linear -> Linear activations as bf16 planes (tensor-core path): band i of a layer whose bands are n[0..10]
+// wide starts mtiles * (chunks of the bands before it) blocks into the buffer.
+struct BandPlanes {
+  char* band[kRealBands];
+  long long lo;
+};
+template <class WidthOf>
+BandPlanes band_planes(const Ws& w, char* buf, WidthOf width_of) {
+  BandPlanes b{};
+  long long chunks = 0;
+  for (int i = 0; i < kRealBands; ++i) {
+    b.band[i] = buf + w.mtiles * chunks * kPlaneBlock;
+    chunks += plane_chunks(width_of(i));
+  }
+  b.lo = w.plane_lo;
+  return b;
+}
+inline void from_planes(LinProb& P, const BandPlanes& b, int i) { P.Ap = b.band[i]; P.a_lo = b.lo; P.A = nullptr; }
+inline void to_planes(LinProb& P, const BandPlanes& b, int i, bool keep_fp32 = false) {
+  P.Op = b.band[i]; P.o_lo = b.lo;
+  if (!keep_fp32) P.O = nullptr;
+}
+inline bool use_planes(long long rows) { return rows >= kTcMinRows && !force_ffma(); }
 
 int single_linear(const void* packed, const Lin& l, const float* A, int lda, float* O, int ldo, long long M, int act,
                   const float* res, int ldres, cudaStream_t s) {
@@ -257,27 +295,42 @@ int run_bandsplit(const float* xf, int ldx, int rows, const void* packed, float*
                   const Ws& w, cudaStream_t s) {
   const Layout& L = layout();
   GroupedArgs g{};
+  const bool pm = use_planes(rows);       // hidden activations as bf16 planes instead of fp32 rows
+  const BandPlanes p_pre0 = band_planes(w, w.planeA, [&](int i) { return L.pre[i][0].N; });
+  const BandPlanes p_res = band_planes(w, w.planeB, [&](int i) { return L.pre[i][1].N; });
+  const BandPlanes p_fc0 = band_planes(w, w.planeA, [&](int i) { return L.fc[i][0].N; });
+  const BandPlanes p_fc1 = band_planes(w, w.planeB, [&](int i) { return L.fc[i][1].N; });
   // pre.0 : x -> bufA (LReLU)
   g.nprob = kRealBands;
-  for (int i = 0; i < kRealBands; ++i)
+  for (int i = 0; i < kRealBands; ++i) {
     set_prob(g.p[i], packed, L.pre[i][0], xf + kBandOff[i], ldx, w.bufA + kBandOff[i], kXS, rows, ACT_LRELU);
+    if (pm) to_planes(g.p[i], p_pre0, i);
+  }
   CK(launch_grouped_linear(g, s));
-  // pre.2 : bufA -> residual (LReLU)
-  for (int i = 0; i < kRealBands; ++i)
+  // pre.2 : bufA -> residual (LReLU); the residual is needed as fp32 rows (decoder) and as the next operand
+  for (int i = 0; i < kRealBands; ++i) {
     set_prob(g.p[i], packed, L.pre[i][1], w.bufA + kBandOff[i], kXS, residual + kBandOff[i], kXS, rows, ACT_LRELU);
+    if (pm) { from_planes(g.p[i], p_pre0, i); to_planes(g.p[i], p_res, i, true); }
+  }
   CK(launch_grouped_linear(g, s));
   mark("pre", s);
   // fc.0 : residual -> hid2 (LReLU)
-  for (int i = 0; i < kRealBands; ++i)
+  for (int i = 0; i < kRealBands; ++i) {
     set_prob(g.p[i], packed, L.fc[i][0], residual + kBandOff[i], kXS, w.hid2 + hid_off(i), kHidStride, rows, ACT_LRELU);
+    if (pm) { from_planes(g.p[i], p_res, i); to_planes(g.p[i], p_fc0, i); }
+  }
   CK(launch_grouped_linear(g, s));
   // fc.2 : hid2 -> featB[:, i, :] (LReLU)
-  for (int i = 0; i < kRealBands; ++i)
+  for (int i = 0; i < kRealBands; ++i) {
     set_prob(g.p[i], packed, L.fc[i][1], w.hid2 + hid_off(i), kHidStride, w.featB + i * kFeat, kBands * kFeat, rows, ACT_LRELU);
+    if (pm) { from_planes(g.p[i], p_fc0, i); to_planes(g.p[i], p_fc1, i); }
+  }
   CK(launch_grouped_linear(g, s));
   // fc.4 : featB -> feat (no activation); band 11 = broadcast of the learned constant (K = 0 problem)
-  for (int i = 0; i < kRealBands; ++i)
+  for (int i = 0; i < kRealBands; ++i) {
     set_prob(g.p[i], packed, L.fc[i][2], w.featB + i * kFeat, kBands * kFeat, feat + i * kFeat, kBands * kFeat, rows, ACT_NONE);
+    if (pm) from_planes(g.p[i], p_fc1, i);
+  }
   {
     LinProb& P = g.p[kRealBands];
     Lin c{};
@@ -384,26 +437,41 @@ int run_decode(const float* feat, const float* residual, const float* xf, int ld
                float* yf, int ldy, const Ws& w, cudaStream_t s) {
   const Layout& L = layout();
   GroupedArgs g{};
+  const bool pm = use_planes(rows);
+  const BandPlanes p_b0 = band_planes(w, w.planeA, [&](int i) { return L.back[i][0].N; });
+  const BandPlanes p_b1 = band_planes(w, w.planeB, [&](int i) { return L.back[i][1].N; });
+  const BandPlanes p_b2 = band_planes(w, w.planeA, [&](int i) { return L.back[i][2].N; });
+  const BandPlanes p_p0 = band_planes(w, w.planeB, [&](int i) { return L.post[i][0].N; });
   g.nprob = kRealBands;
-  for (int i = 0; i < kRealBands; ++i)
+  for (int i = 0; i < kRealBands; ++i) {
     set_prob(g.p[i], packed, L.back[i][0], feat + i * kFeat, kBands * kFeat, w.hid1 + i * kMaskHidden,
              kRealBands * kMaskHidden, rows, ACT_LRELU);
+    if (pm) to_planes(g.p[i], p_b0, i);
+  }
   CK(launch_grouped_linear(g, s));
-  for (int i = 0; i < kRealBands; ++i)
+  for (int i = 0; i < kRealBands; ++i) {
     set_prob(g.p[i], packed, L.back[i][1], w.hid1 + i * kMaskHidden, kRealBands * kMaskHidden, w.hid2 + hid_off(i),
              kHidStride, rows, ACT_LRELU);
+    if (pm) { from_planes(g.p[i], p_b0, i); to_planes(g.p[i], p_b1, i); }
+  }
   CK(launch_grouped_linear(g, s));
-  for (int i = 0; i < kRealBands; ++i)
+  for (int i = 0; i < kRealBands; ++i) {
     set_prob(g.p[i], packed, L.back[i][2], w.hid2 + hid_off(i), kHidStride, w.bufA + kBandOff[i], kXS, rows, ACT_LRELU);
+    if (pm) { from_planes(g.p[i], p_b1, i); to_planes(g.p[i], p_b2, i); }
+  }
   CK(launch_grouped_linear(g, s));
   mark("back", s);
-  for (int i = 0; i < kRealBands; ++i)
+  for (int i = 0; i < kRealBands; ++i) {
     set_prob(g.p[i], packed, L.post[i][0], w.bufA + kBandOff[i], kXS, w.bufB + kBandOff[i], kXS, rows, ACT_LRELU);
+    if (pm) { from_planes(g.p[i], p_b2, i); to_planes(g.p[i], p_p0, i); }
+  }
   CK(launch_grouped_linear(g, s));
   // post.2 : y = x * (residual + W.b + bias)
-  for (int i = 0; i < kRealBands; ++i)
+  for (int i = 0; i < kRealBands; ++i) {
     set_prob(g.p[i], packed, L.post[i][1], w.bufB + kBandOff[i], kXS, yf + kBandOff[i], ldy, rows, ACT_NONE,
              residual + kBandOff[i], kXS, xf + kBandOff[i], ldx);
+    if (pm) from_planes(g.p[i], p_p0, i);
+  }
   CK(launch_grouped_linear(g, s));
   mark("post_mask", s);
   return 0;

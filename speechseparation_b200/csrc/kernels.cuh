@@ -30,8 +30,17 @@ struct LinProb {
   int act;
   int tile_start;      // first tile index of this problem in the launch
   int tiles_n;
+  // Tensor-core path only: activations that go from one Linear straight into the next never exist as fp32
+  // rows. The producing epilogue writes them as "planes": bf16 hi and lo (x = hi + lo), blocked as
+  // [m-tile of 128 rows][k-chunk of 64 columns][128 rows x 128 B, SWIZZLE_128B] = the shared-memory image the
+  // consuming layer's tcgen05.mma reads, so its A operand is two 16 KB bulk copies per chunk (plane_blocks()).
+  const void* Ap;      // optional input planes (hi at Ap, lo at Ap + a_lo); A may then be null
+  void* Op;            // optional output planes (hi at Op, lo at Op + o_lo); O may then be null
+  long long a_lo, o_lo;
 };
 constexpr int kMaxProb = 12;
+constexpr int kPlaneBlock = 128 * 128;                                   // bytes of one [128 x 64] bf16 block
+inline int plane_chunks(int n) { return (n + 63) / 64; }
 struct GroupedArgs {
   LinProb p[kMaxProb];
   int nprob;

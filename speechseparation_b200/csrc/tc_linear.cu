@@ -32,6 +32,7 @@
 // coalesced loads, cheaper conversion and SMSP placement of the roles all left that period
 // unchanged, a TMEM-resident A operand (lstm_tc.cu style) lost more to row-per-thread loads than
 // it saved. The remaining lever is the CTA pair (cta_group::2: half of W per SM) - next round.
+#include <cstdlib>
 #include "kernels.cuh"
 #include "ptx.cuh"
 
@@ -47,24 +48,30 @@ constexpr int STAGES = 2;
 constexpr int A_PLANE = BM * 128;            // bytes of one A plane per stage (16 KB)
 constexpr int W_PLANE = BN_MAX * 128;        // bytes of one W plane per stage (32 KB)
 constexpr int STAGE_BYTES = 2 * A_PLANE + 2 * W_PLANE;   // 96 KB
-constexpr int STG_LD = 36;                              // staging row stride (floats): conflict-free 16B access
-constexpr int STG_WARP = 32 * STG_LD * 4;               // bytes of one epilogue warp's 32x32 staging tile
-// Warp roles are placed by scheduler (SMSP = warp % 4). The thread that issues tcgen05.mma occupies its
-// SMSP's dispatch port for the whole MMA batch (pipeline trace: warps sharing that SMSP made no
-// progress while a batch was being issued), so no producer shares the MMA warp's SMSP:
-//   warp 0            MMA issuer (SMSP 0)          warps 4, 8      idle
-//   warps 1-3,5-7,9,10  A producers (SMSPs 1-3)    warp 11         W loader
-//   warps 12-15       epilogue (TMEM lane quarter = warp % 4)
-constexpr int N_A_WARPS = 8, N_EPI_WARPS = 4;
-constexpr int W_WARP = 11, EPI_WARP0 = 12;
-__device__ __forceinline__ int producer_rank(int warp) {      // 1,2,3,5,6,7,9,10 -> 0..7 ; others -1
-  if ((warp & 3) == 0 || warp > 10) return -1;
-  return (warp >> 2) * 3 + (warp & 3) - 1;
-}
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + N_EPI_WARPS * STG_WARP + 1024;  // + alignment slack
-constexpr int MMA_WARP = 0;
-constexpr int THREADS = 16 * 32;
-constexpr int N_PRODUCERS = N_A_WARPS * 32;                   // 256
+// Warp roles (setmaxnreg works per warpgroup = 4 consecutive warps):
+//   fp32-row A (A_PLANES = false), 24 warps at 80 registers:
+//     warps 0-7   A producer group 0 (fills stage 0)      warps 8-15  A producer group 1 (fills stage 1)
+//     warp 16     MMA issuer (+ TMEM alloc)               warp 17     loader            warps 18, 19 idle
+//     warps 20-23 epilogue, grown to 152 registers
+//   plane A (A_PLANES = true), 12 warps, no register re-partitioning needed:
+//     warp 0 MMA issuer, warp 1 loader (A and W by bulk copy), warps 2, 3 idle, warps 4-11 epilogue
+// An epilogue warp may read the TMEM lane quarter warp % 4; with 8 epilogue warps the two warps of a quarter
+// take alternate 32-column chunks.
+// Two producer groups, each with its own register-resident chunk in flight: the global-load latency of one
+// group's chunk overlaps the convert+store of the other's, and 16 warps of LDG.128 sustain ~2x the bytes per
+// clock of 8 (tools/mem_bench.cu: 12.6 -> 22.3 B/clk/SM from DRAM, 17.3 -> 31.6 from L2).
+constexpr int N_GROUP_WARPS = 8;
+template <bool A_PLANES> struct Roles {
+  static constexpr int PROD_WARPS = A_PLANES ? 0 : 2 * N_GROUP_WARPS;
+  static constexpr int MMA_WARP = PROD_WARPS, LOAD_WARP = PROD_WARPS + 1;
+  static constexpr int EPI_WARP0 = PROD_WARPS + 4;
+  static constexpr int N_EPI_WARPS = A_PLANES ? 8 : 4;
+  static constexpr int THREADS = (EPI_WARP0 + N_EPI_WARPS) * 32;
+};
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024;       // + alignment slack
+constexpr int N_PRODUCERS = N_GROUP_WARPS * 32;               // 256 threads fill one stage
+constexpr int REGS_PRODUCER = 72, REGS_CONTROL = 40, REGS_EPILOGUE = 152;   // released 512*8 + 128*40 = taken 128*72
+static_assert(STAGES == 2, "one producer group per stage");
 constexpr int TMEM_COLS = 512;       // 2 accumulators x 256 fp32 columns
 
 struct TcProb {
@@ -75,6 +82,10 @@ struct TcProb {
   float* O;
   const float* res;
   const float* mul;
+  const uint8_t* Ah;         // A as blocked bf16 planes (kernels.cuh LinProb::Ap), or null: fp32 rows at A
+  const uint8_t* Al;
+  uint8_t* Oh;               // output planes, or null
+  uint8_t* Ol;
   int lda, ldw, ldo, ldres, ldmul;
   int M, N, K, act;
   int tile_start, tiles_m;
@@ -83,6 +94,7 @@ struct TcArgs {
   TcProb p[kMaxProb];
   int nprob;
   int total_tiles;
+  int trace;          // debug builds: this launch records the pipeline timeline
 };
 
 struct Tile {
@@ -151,14 +163,17 @@ __device__ __forceinline__ void store_a(const AChunk& a, uint8_t* a_hi, uint8_t*
 
 __device__ __forceinline__ float lrelu(float v) { return v > 0.f ? v : v * 0.01f; }
 
+#ifndef BSB_TRACE_EPI
+#define BSB_TRACE_EPI 0     // which epilogue warp the trace follows
+#endif
 #ifdef BSB_TRACE
-// pipeline timeline of CTA 0 (debug builds only): three role regions of 3000 (code, clock) pairs,
+// pipeline timeline of CTA 0 (debug builds only): five role regions of 3000 (code, clock) pairs,
 // a private counter per role (no atomics: tracing must not stretch the pipeline it observes)
 __device__ unsigned long long* g_trace = nullptr;
 #define TRACE_DECL int trace_n = 0
 #define TRACE(role, code)                                                            \
   do {                                                                               \
-    if (blockIdx.x == 0 && g_trace != nullptr && trace_n < 3000) {                   \
+    if (blockIdx.x == 0 && args.trace && g_trace != nullptr && trace_n < 3000) {                   \
       g_trace[(role) * 6000 + 2 * trace_n] = (unsigned long long)(code);             \
       g_trace[(role) * 6000 + 2 * trace_n + 1] = (unsigned long long)clock64();      \
       ++trace_n;                                                                     \
@@ -169,8 +184,14 @@ __device__ unsigned long long* g_trace = nullptr;
 #define TRACE(role, code)
 #endif
 
-__global__ void __launch_bounds__(THREADS, 1)
+
+// A_PLANES: every problem of the launch takes its A operand from bf16 planes (two bulk copies per chunk by the
+// loader thread); the 16 producer warps then have no work and only the loader arrives on the full barrier.
+template <bool A_PLANES>
+__global__ void __launch_bounds__(Roles<A_PLANES>::THREADS, 1)
 tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
+  using R = Roles<A_PLANES>;
+  constexpr int MMA_WARP = R::MMA_WARP, W_WARP = R::LOAD_WARP, EPI_WARP0 = R::EPI_WARP0, N_EPI_WARPS = R::N_EPI_WARPS;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bar_full[STAGES], bar_empty[STAGES], bar_tfull[2], bar_tempty[2];
   __shared__ uint32_t tmem_slot;
@@ -183,7 +204,7 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
 
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) {
-      mbar_init(smem_u32(&bar_full[s]), N_PRODUCERS + 1);   // + the W issuer's expect_tx arrive
+      mbar_init(smem_u32(&bar_full[s]), A_PLANES ? 1 : N_PRODUCERS + 1);   // the loader's expect_tx arrive (+ producers)
       mbar_init(smem_u32(&bar_empty[s]), 1);
     }
     for (int a = 0; a < 2; ++a) {
@@ -202,48 +223,46 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
   const uint32_t tmem_base = tmem_slot;
   TRACE_DECL;
 
-  const int prank = producer_rank(warp);
-  if (prank >= 0) {
-    // ================= A producers =================
-    const int pt = prank * 32 + lane;           // producer thread 0..255
-    // One K chunk of A is prefetched into registers while the previous one is converted and stored.
-    // (Two chunks in flight were measured and did not help: at this tile shape the kernel is bound by
-    // the bytes each SM must pull from L2 - 32 KB of A plus 64 KB of W per 128x256x64 chunk - not by
-    // the latency of any one of them; see DESIGN.md.)
-    int stage = 0;
-    uint32_t phase = 0;
+  if (warp < R::PROD_WARPS) {
+    // ================= A producers: group g owns stage g = every second K chunk of the CTA's chunk stream ====
+    setmaxnreg_dec<REGS_PRODUCER>();
+    const int grp = warp / N_GROUP_WARPS;
+    const int pt = (warp % N_GROUP_WARPS) * 32 + lane;      // thread 0..255 of the group
+    const uint32_t full = smem_u32(&bar_full[grp]), empty = smem_u32(&bar_empty[grp]);
+    uint8_t* sb = smem_gen + grp * STAGE_BYTES;
     int tile = blockIdx.x, kc = 0, nk = 0;
     Tile T{};
-    AChunk regs;
-    if (tile < args.total_tiles) {
-      T = decode_tile(args, tile);
-      nk = (args.p[T.pi].K + BK - 1) / BK;
-      load_a(args.p[T.pi], T.m0, 0, pt, regs);
-    }
-    while (tile < args.total_tiles) {
-      mbar_wait(smem_u32(&bar_empty[stage]), phase ^ 1);
-      if (pt == 0) TRACE(0, 1);
-      uint8_t* sb = smem_gen + stage * STAGE_BYTES;
-      store_a(regs, sb, sb + A_PLANE, pt);
-      if (pt == 0) TRACE(0, 2);
-      fence_proxy_async_smem();
-      mbar_arrive(smem_u32(&bar_full[stage]));
-      if (pt == 0) TRACE(0, 3);
-      if (++stage == STAGES) { stage = 0; phase ^= 1; }
-      if (++kc == nk) {
-        kc = 0;
-        tile += gridDim.x;
-        if (tile < args.total_tiles) {
-          T = decode_tile(args, tile);
-          nk = (args.p[T.pi].K + BK - 1) / BK;
-        }
+    auto open_tile = [&]() {
+      if (tile < args.total_tiles) {
+        T = decode_tile(args, tile);
+        nk = (args.p[T.pi].K + BK - 1) / BK;
       }
+    };
+    auto next_chunk = [&]() {
+      if (++kc == nk) { kc = 0; tile += gridDim.x; open_tile(); }
+    };
+    open_tile();
+    if (grp == 1 && tile < args.total_tiles) next_chunk();
+    uint32_t phase = 0;
+    AChunk regs;
+    if (tile < args.total_tiles) load_a(args.p[T.pi], T.m0, kc * BK, pt, regs);
+    while (tile < args.total_tiles) {
+      mbar_wait(empty, phase ^ 1);
+      if (pt == 0) TRACE(grp ? 3 : 0, 1 + 100 * grp);
+      store_a(regs, sb, sb + A_PLANE, pt);
+      fence_proxy_async_smem();
+      mbar_arrive(full);
+      if (pt == 0) TRACE(grp ? 3 : 0, 3 + 100 * grp);
+      phase ^= 1;
+      next_chunk();
+      if (tile < args.total_tiles) next_chunk();
       if (tile < args.total_tiles) load_a(args.p[T.pi], T.m0, kc * BK, pt, regs);
-      if (pt == 0) TRACE(0, 4);
+      if (pt == 0) TRACE(grp ? 3 : 0, 4 + 100 * grp);
     }
-  } else if (warp == W_WARP) {
-    // ================= W loader (one thread) =================
-    if (lane == 0) {
+  } else if (warp < EPI_WARP0) {
+    if (!A_PLANES) setmaxnreg_dec<REGS_CONTROL>();
+    if (warp == W_WARP && lane == 0) {
+      // ================= W loader (one thread) =================
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
@@ -252,18 +271,23 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
         const int nk = (P.K + BK - 1) / BK;
         for (int kc = 0; kc < nk; ++kc) {
           mbar_wait(smem_u32(&bar_empty[stage]), phase ^ 1);
+          TRACE(4, 30 + stage);
           // W blocks [bn x 64] bf16, already swizzled: (n0 * nch + kc * bn) * 128 bytes into each plane
           const uint32_t bytes = (uint32_t)T.bn * 128u;
           const long long off = ((long long)T.n0 * (P.ldw >> 6) + (long long)kc * T.bn) * 128;
           const uint32_t bar = smem_u32(&bar_full[stage]);
-          mbar_arrive_expect_tx(bar, 2 * bytes);
+          mbar_arrive_expect_tx(bar, 2 * bytes + (A_PLANES ? 2 * A_PLANE : 0));
+          if (A_PLANES) {
+            const long long aoff = ((long long)(T.m0 / BM) * nk + kc) * A_PLANE;
+            bulk_g2s(smem_base + stage * STAGE_BYTES, P.Ah + aoff, A_PLANE, bar);
+            bulk_g2s(smem_base + stage * STAGE_BYTES + A_PLANE, P.Al + aoff, A_PLANE, bar);
+          }
           bulk_g2s(smem_base + stage * STAGE_BYTES + 2 * A_PLANE, reinterpret_cast<const uint8_t*>(P.Wh) + off, bytes, bar);
           bulk_g2s(smem_base + stage * STAGE_BYTES + 2 * A_PLANE + W_PLANE, reinterpret_cast<const uint8_t*>(P.Wl) + off, bytes, bar);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
-    }
-  } else if (warp == MMA_WARP) {
+    } else if (warp == MMA_WARP) {
     // ================= MMA issuer =================
     int stage = 0, acc = 0;
     uint32_t phase = 0, acc_phase = 0;
@@ -302,102 +326,118 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
-  } else if (warp >= EPI_WARP0) {
+    }
+  } else {
     // ================= epilogue =================
-    const int q = warp & 3;                 // TMEM lane quarter this warp may access
-    float* stg = reinterpret_cast<float*>(smem_gen + STAGES * STAGE_BYTES + (warp - EPI_WARP0) * STG_WARP);
-    const int cg = lane & 7, sub = lane >> 3;   // transposed phase: 4 columns at 4*cg of rows sub + 4k
+    // One thread = one accumulator row (TMEM lane), 32 consecutive columns per step, no transposition:
+    // the row's 32 columns go out as 16-byte pieces of one 128-byte line (fp32 rows: 8 stores; planes: 4 + 4),
+    // L2 merges the pieces. A single warp is bound by instruction latency (~4 cycles per dependent instruction),
+    // so the instruction count per column is what matters here, not the store pattern.
+    if (!A_PLANES) setmaxnreg_inc<REGS_EPILOGUE>();
+    const int ew = warp - EPI_WARP0;
+    const int q = ew & 3;                   // TMEM lane quarter this warp may access (EPI_WARP0 % 4 == 0)
+    constexpr int CC_STEP = N_EPI_WARPS / 4;
+    const int rt = q * 32 + lane;           // row of the tile
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
       const Tile T = decode_tile(args, tile);
       const TcProb& P = args.p[T.pi];
       mbar_wait(smem_u32(&bar_tfull[acc]), acc_phase);
-      if (warp == EPI_WARP0 && lane == 0) TRACE(2, 20);
+      if (ew == BSB_TRACE_EPI && lane == 0) TRACE(2, 20);
       tc_fence_after();
-      const int mw = T.m0 + q * 32;           // first row of this warp
-      const bool o_vec = ((P.ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.O) & 15) == 0);
-      const bool r_vec = P.res && ((P.ldres & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.res) & 15) == 0);
-      const bool m_vec = P.mul && ((P.ldmul & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.mul) & 15) == 0);
+      const int m = T.m0 + rt;
+      const bool row = m < P.M;
+      const float* rrow = P.res ? P.res + (long long)m * P.ldres : nullptr;
+      const float* mrow = P.mul ? P.mul + (long long)m * P.ldmul : nullptr;
+      float* orow = P.O ? P.O + (long long)m * P.ldo : nullptr;
+      // 16-byte access needs 16-byte aligned rows (band offsets 2 and 6 floats are not)
+      const bool r_vec = rrow && ((P.ldres & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.res) & 15) == 0);
+      const bool m_vec = mrow && ((P.ldmul & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.mul) & 15) == 0);
+      const bool o_vec = orow && ((P.ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.O) & 15) == 0);
       const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN_MAX);
-      for (int cc = 0; cc < T.bn / 32; ++cc) {
+      const int nch_o = (P.N + 63) >> 6;       // 64-column chunks per row block of the output planes
+      for (int cc = ew >> 2; cc < T.bn / 32; cc += CC_STEP) {
         const int nb = T.n0 + cc * 32;
-        if (nb >= P.N) break;
-        // operands of the fused "+ residual" / "* x": all loads of the chunk are issued up front
-        const int n = nb + 4 * cg;
-        const bool ncol = n < P.N;
-        const bool full4 = n + 3 < P.N;
-        float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
-        float4 rr[8], mm[8];
-        if (ncol) bb = __ldg(reinterpret_cast<const float4*>(P.bias + n));   // bias padded to Npad
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const int m = mw + sub + 4 * k;
-          rr[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-          mm[k] = make_float4(1.f, 1.f, 1.f, 1.f);
-          if (ncol && m < P.M) {
-            if (P.res) {
-              const float* rrow = P.res + (long long)m * P.ldres + n;
-              if (r_vec && full4) {
-                rr[k] = __ldg(reinterpret_cast<const float4*>(rrow));
-              } else {
-                rr[k].x = __ldg(rrow);
-                if (n + 1 < P.N) rr[k].y = __ldg(rrow + 1);
-                if (n + 2 < P.N) rr[k].z = __ldg(rrow + 2);
-                if (n + 3 < P.N) rr[k].w = __ldg(rrow + 3);
-              }
-            }
-            if (P.mul) {
-              const float* mrow = P.mul + (long long)m * P.ldmul + n;
-              if (m_vec && full4) {
-                mm[k] = __ldg(reinterpret_cast<const float4*>(mrow));
-              } else {
-                mm[k].x = __ldg(mrow);
-                if (n + 1 < P.N) mm[k].y = __ldg(mrow + 1);
-                if (n + 2 < P.N) mm[k].z = __ldg(mrow + 2);
-                if (n + 3 < P.N) mm[k].w = __ldg(mrow + 3);
-              }
-            }
-          }
-        }
+        if (nb >= P.N && P.Oh == nullptr) break;   // fp32 rows stop at N; planes carry the zero padding to 64
         uint32_t r[32];
         tmem_ld_32x32(tbase + cc * 32, r);
-        tmem_ld_wait();
+        float v[32];
+        // bias (zero padded to Npad >= n0 + bn; same address in every lane: one L1 transaction per load)
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          *reinterpret_cast<uint4*>(stg + lane * STG_LD + 4 * j) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
-        __syncwarp();
-        if (ncol) {
+        for (int j = 0; j < 8; ++j) {
+          const float4 b4 = __ldg(reinterpret_cast<const float4*>(P.bias + nb) + j);
+          v[4 * j] = b4.x; v[4 * j + 1] = b4.y; v[4 * j + 2] = b4.z; v[4 * j + 3] = b4.w;
+        }
+        tmem_ld_wait32(r);
+        if (ew == BSB_TRACE_EPI && lane == 0) TRACE(2, 23);
+        if (P.act == ACT_LRELU) {
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            const int i = sub + 4 * k;
-            const int m = mw + i;
-            const float4 a4 = *reinterpret_cast<const float4*>(stg + i * STG_LD + 4 * cg);
-            float v[4] = {a4.x + bb.x, a4.y + bb.y, a4.z + bb.z, a4.w + bb.w};
-            if (P.act == ACT_LRELU) {
+          for (int j = 0; j < 32; ++j) v[j] = lrelu(v[j] + __uint_as_float(r[j]));
+        } else {
 #pragma unroll
-              for (int e = 0; e < 4; ++e) v[e] = lrelu(v[e]);
-            }
-            v[0] = (v[0] + rr[k].x) * mm[k].x;
-            v[1] = (v[1] + rr[k].y) * mm[k].y;
-            v[2] = (v[2] + rr[k].z) * mm[k].z;
-            v[3] = (v[3] + rr[k].w) * mm[k].w;
-            if (m < P.M) {
-              float* orow = P.O + (long long)m * P.ldo + n;
-              if (o_vec && full4) {
-                *reinterpret_cast<float4*>(orow) = make_float4(v[0], v[1], v[2], v[3]);
+          for (int j = 0; j < 32; ++j) v[j] += __uint_as_float(r[j]);
+        }
+        if (row) {
+          if (rrow) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const int n = nb + 4 * j;
+              if (r_vec && n + 3 < P.N) {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(rrow + n));
+                v[4 * j] += t.x; v[4 * j + 1] += t.y; v[4 * j + 2] += t.z; v[4 * j + 3] += t.w;
               } else {
 #pragma unroll
-                for (int e = 0; e < 4; ++e) if (n + e < P.N) orow[e] = v[e];
+                for (int e = 0; e < 4; ++e) if (n + e < P.N) v[4 * j + e] += __ldg(rrow + n + e);
               }
             }
           }
+          if (mrow) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const int n = nb + 4 * j;
+              if (m_vec && n + 3 < P.N) {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(mrow + n));
+                v[4 * j] *= t.x; v[4 * j + 1] *= t.y; v[4 * j + 2] *= t.z; v[4 * j + 3] *= t.w;
+              } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) if (n + e < P.N) v[4 * j + e] *= __ldg(mrow + n + e);
+              }
+            }
+          }
+          if (orow) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const int n = nb + 4 * j;
+              if (o_vec && n + 3 < P.N) {
+                *reinterpret_cast<float4*>(orow + n) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+              } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) if (n + e < P.N) orow[n + e] = v[4 * j + e];
+              }
+            }
+          }
+          if (P.Oh) {
+            // block (m-tile, 64-column chunk); this step covers 16-byte units (cc&1)*4 .. +3 of row rt
+            const long long blk = ((long long)(T.m0 / BM) * nch_o + (nb >> 6)) * A_PLANE;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              uint4 h, l;
+              split2(v[8 * u], v[8 * u + 1], h.x, l.x);
+              split2(v[8 * u + 2], v[8 * u + 3], h.y, l.y);
+              split2(v[8 * u + 4], v[8 * u + 5], h.z, l.z);
+              split2(v[8 * u + 6], v[8 * u + 7], h.w, l.w);
+              const uint32_t off = sw128(rt, ((cc & 1) << 2) + u);
+              *reinterpret_cast<uint4*>(P.Oh + blk + off) = h;
+              *reinterpret_cast<uint4*>(P.Ol + blk + off) = l;
+            }
+          }
         }
-        __syncwarp();
+        if (ew == BSB_TRACE_EPI && lane == 0) TRACE(2, 24);
       }
       tc_fence_before();
       mbar_arrive(smem_u32(&bar_tempty[acc]));
-      if (warp == EPI_WARP0 && lane == 0) TRACE(2, 21);
+      if (ew == BSB_TRACE_EPI && lane == 0) TRACE(2, 21);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   }
@@ -419,7 +459,9 @@ int g_sm_count[64] = {};
 cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(tc_grouped_linear_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(tc_grouped_linear_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(tc_grouped_linear_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
@@ -440,10 +482,15 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
       const int t = order[j]; order[j] = order[j - 1]; order[j - 1] = t;
     }
   TcArgs ta{};
-  int total = 0;
+  int total = 0, n_planes = 0;
   for (int i = 0; i < n; ++i) {
     const LinProb& L = args.p[order[i]];
     TcProb& P = ta.p[i];
+    P.Ah = reinterpret_cast<const uint8_t*>(L.Ap);
+    P.Al = L.Ap ? P.Ah + L.a_lo : nullptr;
+    P.Oh = reinterpret_cast<uint8_t*>(L.Op);
+    P.Ol = L.Op ? P.Oh + L.o_lo : nullptr;
+    n_planes += L.Ap != nullptr;
     P.A = L.A; P.Wh = reinterpret_cast<const __nv_bfloat16*>(L.Wh); P.Wl = reinterpret_cast<const __nv_bfloat16*>(L.Wl);
     P.bias = L.bias; P.O = L.O; P.res = L.res; P.mul = L.mul;
     P.lda = L.lda; P.ldw = L.ldw64; P.ldo = L.ldo; P.ldres = L.ldres; P.ldmul = L.ldmul;
@@ -454,9 +501,19 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
   }
   ta.nprob = n;
   ta.total_tiles = total;
+#ifdef BSB_TRACE
+  static int trace_launch = 0, trace_sel = -2;
+  if (trace_sel == -2) trace_sel = getenv("BSB_TRACE_LAUNCH") ? atoi(getenv("BSB_TRACE_LAUNCH")) : -1;
+  ta.trace = (trace_launch++ == trace_sel);
+#endif
+
   if (total == 0) return cudaSuccess;
+  if (n_planes != 0 && n_planes != n) return cudaErrorInvalidValue;   // one A source per launch
   const int grid = total < sms ? total : sms;
-  tc_grouped_linear_kernel<<<grid, THREADS, SMEM_BYTES, s>>>(ta);
+  if (n_planes)
+    tc_grouped_linear_kernel<true><<<grid, Roles<true>::THREADS, SMEM_BYTES, s>>>(ta);
+  else
+    tc_grouped_linear_kernel<false><<<grid, Roles<false>::THREADS, SMEM_BYTES, s>>>(ta);
   count_launch();
   return cudaGetLastError();
 }
