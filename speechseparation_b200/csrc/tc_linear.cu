@@ -68,7 +68,7 @@ template <bool A_PLANES> struct Roles {
   static constexpr int N_EPI_WARPS = A_PLANES ? 8 : 4;
   static constexpr int THREADS = (EPI_WARP0 + N_EPI_WARPS) * 32;
 };
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024;       // + alignment slack
+template <bool A_PLANES> constexpr int smem_bytes() { return STAGES * STAGE_BYTES + 1024; }   // + alignment slack
 constexpr int N_PRODUCERS = N_GROUP_WARPS * 32;               // 256 threads fill one stage
 constexpr int REGS_PRODUCER = 72, REGS_CONTROL = 40, REGS_EPILOGUE = 152;   // released 512*8 + 128*40 = taken 128*72
 static_assert(STAGES == 2, "one producer group per stage");
@@ -329,10 +329,13 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
     }
   } else {
     // ================= epilogue =================
-    // One thread = one accumulator row (TMEM lane), 32 consecutive columns per step, no transposition:
-    // the row's 32 columns go out as 16-byte pieces of one 128-byte line (fp32 rows: 8 stores; planes: 4 + 4),
-    // L2 merges the pieces. A single warp is bound by instruction latency (~4 cycles per dependent instruction),
-    // so the instruction count per column is what matters here, not the store pattern.
+    // tcgen05.ld gives one thread one accumulator row (TMEM lane), 32 consecutive columns per step, and the
+    // row is written from that layout: fp32 rows as eight 16-byte pieces of one 128-byte line, planes as four
+    // 16-byte units per plane; L2 merges the pieces. (A transposition through shared memory so that a request
+    // covers whole lines was measured slower: a single warp runs at ~4 cycles per dependent instruction, so
+    // the instruction count and the exposed load latency per column bound the epilogue, not the store pattern.)
+    // The "+ residual" / "* x" operands of a step are requested one step ahead - for the first step of a tile
+    // before the accumulator is waited for - so their latency overlaps the main loop.
     if (!A_PLANES) setmaxnreg_inc<REGS_EPILOGUE>();
     const int ew = warp - EPI_WARP0;
     const int q = ew & 3;                   // TMEM lane quarter this warp may access (EPI_WARP0 % 4 == 0)
@@ -343,23 +346,55 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
     for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
       const Tile T = decode_tile(args, tile);
       const TcProb& P = args.p[T.pi];
+      const int m = T.m0 + rt;
+      const bool row = m < P.M;
+      const float* rrow = (P.res && row) ? P.res + (long long)m * P.ldres : nullptr;
+      const float* mrow = (P.mul && row) ? P.mul + (long long)m * P.ldmul : nullptr;
+      float* orow = (P.O && row) ? P.O + (long long)m * P.ldo : nullptr;
+      // 16-byte access needs 16-byte aligned rows (band offsets 2 and 6 floats are not)
+      const bool r_vec = ((P.ldres & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.res) & 15) == 0);
+      const bool m_vec = ((P.ldmul & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.mul) & 15) == 0);
+      const bool o_vec = ((P.ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.O) & 15) == 0);
+      const int ncc = (P.Oh != nullptr) ? T.bn / 32 : min(T.bn / 32, (P.N - T.n0 + 31) / 32);   // planes carry the zero padding
+      float4 pr[8], pm[8];
+      auto fetch = [&](int nb) {             // residual / multiplier columns nb..nb+31 of this thread's row
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int n = nb + 4 * j;
+          pr[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+          pm[j] = make_float4(1.f, 1.f, 1.f, 1.f);
+          if (rrow) {
+            if (r_vec && n + 3 < P.N) {
+              pr[j] = __ldg(reinterpret_cast<const float4*>(rrow + n));
+            } else {
+              if (n < P.N) pr[j].x = __ldg(rrow + n);
+              if (n + 1 < P.N) pr[j].y = __ldg(rrow + n + 1);
+              if (n + 2 < P.N) pr[j].z = __ldg(rrow + n + 2);
+              if (n + 3 < P.N) pr[j].w = __ldg(rrow + n + 3);
+            }
+          }
+          if (mrow) {
+            if (m_vec && n + 3 < P.N) {
+              pm[j] = __ldg(reinterpret_cast<const float4*>(mrow + n));
+            } else {
+              if (n < P.N) pm[j].x = __ldg(mrow + n);
+              if (n + 1 < P.N) pm[j].y = __ldg(mrow + n + 1);
+              if (n + 2 < P.N) pm[j].z = __ldg(mrow + n + 2);
+              if (n + 3 < P.N) pm[j].w = __ldg(mrow + n + 3);
+            }
+          }
+        }
+      };
+      const bool has_rm = rrow != nullptr || mrow != nullptr;
+      int cc = ew >> 2;
+      if (has_rm && cc < ncc) fetch(T.n0 + cc * 32);
       mbar_wait(smem_u32(&bar_tfull[acc]), acc_phase);
       if (ew == BSB_TRACE_EPI && lane == 0) TRACE(2, 20);
       tc_fence_after();
-      const int m = T.m0 + rt;
-      const bool row = m < P.M;
-      const float* rrow = P.res ? P.res + (long long)m * P.ldres : nullptr;
-      const float* mrow = P.mul ? P.mul + (long long)m * P.ldmul : nullptr;
-      float* orow = P.O ? P.O + (long long)m * P.ldo : nullptr;
-      // 16-byte access needs 16-byte aligned rows (band offsets 2 and 6 floats are not)
-      const bool r_vec = rrow && ((P.ldres & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.res) & 15) == 0);
-      const bool m_vec = mrow && ((P.ldmul & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.mul) & 15) == 0);
-      const bool o_vec = orow && ((P.ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.O) & 15) == 0);
       const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN_MAX);
       const int nch_o = (P.N + 63) >> 6;       // 64-column chunks per row block of the output planes
-      for (int cc = ew >> 2; cc < T.bn / 32; cc += CC_STEP) {
+      for (; cc < ncc; cc += CC_STEP) {
         const int nb = T.n0 + cc * 32;
-        if (nb >= P.N && P.Oh == nullptr) break;   // fp32 rows stop at N; planes carry the zero padding to 64
         uint32_t r[32];
         tmem_ld_32x32(tbase + cc * 32, r);
         float v[32];
@@ -378,59 +413,41 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] += __uint_as_float(r[j]);
         }
-        if (row) {
-          if (rrow) {
+        if (has_rm) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const int n = nb + 4 * j;
-              if (r_vec && n + 3 < P.N) {
-                const float4 t = __ldg(reinterpret_cast<const float4*>(rrow + n));
-                v[4 * j] += t.x; v[4 * j + 1] += t.y; v[4 * j + 2] += t.z; v[4 * j + 3] += t.w;
-              } else {
+          for (int j = 0; j < 8; ++j) {
+            v[4 * j] = (v[4 * j] + pr[j].x) * pm[j].x;
+            v[4 * j + 1] = (v[4 * j + 1] + pr[j].y) * pm[j].y;
+            v[4 * j + 2] = (v[4 * j + 2] + pr[j].z) * pm[j].z;
+            v[4 * j + 3] = (v[4 * j + 3] + pr[j].w) * pm[j].w;
+          }
+          if (cc + CC_STEP < ncc) fetch(nb + CC_STEP * 32);
+        }
+        if (orow) {
 #pragma unroll
-                for (int e = 0; e < 4; ++e) if (n + e < P.N) v[4 * j + e] += __ldg(rrow + n + e);
-              }
+          for (int j = 0; j < 8; ++j) {
+            const int n = nb + 4 * j;
+            if (o_vec && n + 3 < P.N) {
+              *reinterpret_cast<float4*>(orow + n) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            } else {
+#pragma unroll
+              for (int e = 0; e < 4; ++e) if (n + e < P.N) orow[n + e] = v[4 * j + e];
             }
           }
-          if (mrow) {
+        }
+        if (P.Oh && row) {
+          // block (m-tile, 64-column chunk); this step covers 16-byte units (cc&1)*4 .. +3 of row rt
+          const long long blk = ((long long)(T.m0 / BM) * nch_o + (nb >> 6)) * A_PLANE;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const int n = nb + 4 * j;
-              if (m_vec && n + 3 < P.N) {
-                const float4 t = __ldg(reinterpret_cast<const float4*>(mrow + n));
-                v[4 * j] *= t.x; v[4 * j + 1] *= t.y; v[4 * j + 2] *= t.z; v[4 * j + 3] *= t.w;
-              } else {
-#pragma unroll
-                for (int e = 0; e < 4; ++e) if (n + e < P.N) v[4 * j + e] *= __ldg(mrow + n + e);
-              }
-            }
-          }
-          if (orow) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const int n = nb + 4 * j;
-              if (o_vec && n + 3 < P.N) {
-                *reinterpret_cast<float4*>(orow + n) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-              } else {
-#pragma unroll
-                for (int e = 0; e < 4; ++e) if (n + e < P.N) orow[n + e] = v[4 * j + e];
-              }
-            }
-          }
-          if (P.Oh) {
-            // block (m-tile, 64-column chunk); this step covers 16-byte units (cc&1)*4 .. +3 of row rt
-            const long long blk = ((long long)(T.m0 / BM) * nch_o + (nb >> 6)) * A_PLANE;
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              uint4 h, l;
-              split2(v[8 * u], v[8 * u + 1], h.x, l.x);
-              split2(v[8 * u + 2], v[8 * u + 3], h.y, l.y);
-              split2(v[8 * u + 4], v[8 * u + 5], h.z, l.z);
-              split2(v[8 * u + 6], v[8 * u + 7], h.w, l.w);
-              const uint32_t off = sw128(rt, ((cc & 1) << 2) + u);
-              *reinterpret_cast<uint4*>(P.Oh + blk + off) = h;
-              *reinterpret_cast<uint4*>(P.Ol + blk + off) = l;
-            }
+          for (int u = 0; u < 4; ++u) {
+            uint4 h, l;
+            split2(v[8 * u], v[8 * u + 1], h.x, l.x);
+            split2(v[8 * u + 2], v[8 * u + 3], h.y, l.y);
+            split2(v[8 * u + 4], v[8 * u + 5], h.z, l.z);
+            split2(v[8 * u + 6], v[8 * u + 7], h.w, l.w);
+            const uint32_t off = sw128(rt, ((cc & 1) << 2) + u);
+            *reinterpret_cast<uint4*>(P.Oh + blk + off) = h;
+            *reinterpret_cast<uint4*>(P.Ol + blk + off) = l;
           }
         }
         if (ew == BSB_TRACE_EPI && lane == 0) TRACE(2, 24);
@@ -459,9 +476,9 @@ int g_sm_count[64] = {};
 cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(tc_grouped_linear_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(tc_grouped_linear_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<false>());
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(tc_grouped_linear_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    e = cudaFuncSetAttribute(tc_grouped_linear_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<true>());
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
@@ -511,9 +528,9 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
   if (n_planes != 0 && n_planes != n) return cudaErrorInvalidValue;   // one A source per launch
   const int grid = total < sms ? total : sms;
   if (n_planes)
-    tc_grouped_linear_kernel<true><<<grid, Roles<true>::THREADS, SMEM_BYTES, s>>>(ta);
+    tc_grouped_linear_kernel<true><<<grid, Roles<true>::THREADS, smem_bytes<true>(), s>>>(ta);
   else
-    tc_grouped_linear_kernel<false><<<grid, Roles<false>::THREADS, SMEM_BYTES, s>>>(ta);
+    tc_grouped_linear_kernel<false><<<grid, Roles<false>::THREADS, smem_bytes<false>(), s>>>(ta);
   count_launch();
   return cudaGetLastError();
 }
