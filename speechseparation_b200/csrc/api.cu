@@ -62,6 +62,7 @@ struct Ws {
   float* yf;        // [R][kXS]
   char* planeA;     // two buffers of bf16 hi/lo planes for Linear -> Linear activations (kernels.cuh LinProb::Ap)
   char* planeB;
+  char* planeR;     // the residual (bandFCs_pre output) when it lives only as planes (fused forward)
   long long plane_lo;   // byte distance hi -> lo plane inside a buffer
   long long mtiles;     // 128-row tiles
 };
@@ -93,6 +94,7 @@ size_t carve(Ws* w, char* base, long long R, bool with_io) {
     const size_t plane_floats = (size_t)mt * kPlaneChunksMax * kPlaneBlock / sizeof(float);
     p = take(2 * plane_floats); if (w) w->planeA = reinterpret_cast<char*>(p);
     p = take(2 * plane_floats); if (w) w->planeB = reinterpret_cast<char*>(p);
+    p = take(2 * plane_floats); if (w) w->planeR = reinterpret_cast<char*>(p);
     if (w) { w->plane_lo = (long long)plane_floats * sizeof(float); w->mtiles = mt; }
   }
   if (with_io) {
@@ -128,7 +130,7 @@ void set_prob(LinProb& P, const void* packed, const Lin& l, const float* A, int 
   P.M = M; P.N = l.N; P.K = l.K;
   P.act = act;
   P.tile_start = 0; P.tiles_n = 0;
-  P.Ap = nullptr; P.Op = nullptr; P.a_lo = P.o_lo = 0;
+  P.Ap = nullptr; P.Op = nullptr; P.Rp = nullptr; P.a_lo = P.o_lo = P.r_lo = 0;
 }
 
 // Linear -> Linear activations as bf16 planes (tensor-core path): band i of a layer whose bands are n[0..10]
@@ -153,6 +155,7 @@ inline void to_planes(LinProb& P, const BandPlanes& b, int i, bool keep_fp32 = f
   P.Op = b.band[i]; P.o_lo = b.lo;
   if (!keep_fp32) P.O = nullptr;
 }
+inline void res_planes(LinProb& P, const BandPlanes& b, int i) { P.Rp = b.band[i]; P.r_lo = b.lo; P.res = nullptr; }
 inline bool use_planes(long long rows) { return rows >= kTcMinRows && !force_ffma(); }
 
 int single_linear(const void* packed, const Lin& l, const float* A, int lda, float* O, int ldo, long long M, int act,
@@ -297,7 +300,11 @@ int run_bandsplit(const float* xf, int ldx, int rows, const void* packed, float*
   GroupedArgs g{};
   const bool pm = use_planes(rows);       // hidden activations as bf16 planes instead of fp32 rows
   const BandPlanes p_pre0 = band_planes(w, w.planeA, [&](int i) { return L.pre[i][0].N; });
-  const BandPlanes p_res = band_planes(w, w.planeB, [&](int i) { return L.pre[i][1].N; });
+  // residual == nullptr (fused forward, plane mode only): the residual exists as planes in planeR, which the
+  // decoder reads back; otherwise fp32 rows for the caller plus planes for the next layer
+  if (residual == nullptr && !pm) return BSB_E_ARG;
+  float* rrows = residual ? residual : w.residual;     // only for pointer arithmetic when the rows are not used
+  const BandPlanes p_res = band_planes(w, residual ? w.planeB : w.planeR, [&](int i) { return L.pre[i][1].N; });
   const BandPlanes p_fc0 = band_planes(w, w.planeA, [&](int i) { return L.fc[i][0].N; });
   const BandPlanes p_fc1 = band_planes(w, w.planeB, [&](int i) { return L.fc[i][1].N; });
   // pre.0 : x -> bufA (LReLU)
@@ -309,14 +316,14 @@ int run_bandsplit(const float* xf, int ldx, int rows, const void* packed, float*
   CK(launch_grouped_linear(g, s));
   // pre.2 : bufA -> residual (LReLU); the residual is needed as fp32 rows (decoder) and as the next operand
   for (int i = 0; i < kRealBands; ++i) {
-    set_prob(g.p[i], packed, L.pre[i][1], w.bufA + kBandOff[i], kXS, residual + kBandOff[i], kXS, rows, ACT_LRELU);
-    if (pm) { from_planes(g.p[i], p_pre0, i); to_planes(g.p[i], p_res, i, true); }
+    set_prob(g.p[i], packed, L.pre[i][1], w.bufA + kBandOff[i], kXS, rrows + kBandOff[i], kXS, rows, ACT_LRELU);
+    if (pm) { from_planes(g.p[i], p_pre0, i); to_planes(g.p[i], p_res, i, residual != nullptr); }
   }
   CK(launch_grouped_linear(g, s));
   mark("pre", s);
   // fc.0 : residual -> hid2 (LReLU)
   for (int i = 0; i < kRealBands; ++i) {
-    set_prob(g.p[i], packed, L.fc[i][0], residual + kBandOff[i], kXS, w.hid2 + hid_off(i), kHidStride, rows, ACT_LRELU);
+    set_prob(g.p[i], packed, L.fc[i][0], rrows + kBandOff[i], kXS, w.hid2 + hid_off(i), kHidStride, rows, ACT_LRELU);
     if (pm) { from_planes(g.p[i], p_res, i); to_planes(g.p[i], p_fc0, i); }
   }
   CK(launch_grouped_linear(g, s));
@@ -442,6 +449,9 @@ int run_decode(const float* feat, const float* residual, const float* xf, int ld
   const BandPlanes p_b1 = band_planes(w, w.planeB, [&](int i) { return L.back[i][1].N; });
   const BandPlanes p_b2 = band_planes(w, w.planeA, [&](int i) { return L.back[i][2].N; });
   const BandPlanes p_p0 = band_planes(w, w.planeB, [&](int i) { return L.post[i][0].N; });
+  const BandPlanes p_rres = band_planes(w, w.planeR, [&](int i) { return L.pre[i][1].N; });
+  if (residual == nullptr && !pm) return BSB_E_ARG;
+  const float* rrows = residual ? residual : w.residual;
   g.nprob = kRealBands;
   for (int i = 0; i < kRealBands; ++i) {
     set_prob(g.p[i], packed, L.back[i][0], feat + i * kFeat, kBands * kFeat, w.hid1 + i * kMaskHidden,
@@ -469,8 +479,9 @@ int run_decode(const float* feat, const float* residual, const float* xf, int ld
   // post.2 : y = x * (residual + W.b + bias)
   for (int i = 0; i < kRealBands; ++i) {
     set_prob(g.p[i], packed, L.post[i][1], w.bufB + kBandOff[i], kXS, yf + kBandOff[i], ldy, rows, ACT_NONE,
-             residual + kBandOff[i], kXS, xf + kBandOff[i], ldx);
+             rrows + kBandOff[i], kXS, xf + kBandOff[i], ldx);
     if (pm) from_planes(g.p[i], p_p0, i);
+    if (residual == nullptr) res_planes(g.p[i], p_rres, i);
   }
   CK(launch_grouped_linear(g, s));
   mark("post_mask", s);
@@ -480,7 +491,8 @@ int run_decode(const float* feat, const float* residual, const float* xf, int ld
 int run_model(const float* xf, int ldx, int C, int T, const void* packed, const float* state, float* new_state,
               float* yf, int ldy, const Ws& w, cudaStream_t s) {
   const int rows = C * T;
-  CKI(run_bandsplit(xf, ldx, rows, packed, w.residual, w.featA, w, s));
+  float* residual = use_planes(rows) ? nullptr : w.residual;     // plane mode: the residual never exists as fp32 rows
+  CKI(run_bandsplit(xf, ldx, rows, packed, residual, w.featA, w, s));
   float* fa = w.featA;
   float* fb = w.featB;
   const long long blk = (long long)4 * C * kBands * kFeat;   // one Timewise block's (h,c) x 2 layers
@@ -494,7 +506,7 @@ int run_model(const float* xf, int ldx, int C, int T, const void* packed, const 
     CKI(run_rnn_block(j, fa, C, T, packed, si, so, fb, w, s));
     float* t = fa; fa = fb; fb = t;
   }
-  CKI(run_decode(fa, w.residual, xf, ldx, rows, packed, yf, ldy, w, s));
+  CKI(run_decode(fa, residual, xf, ldx, rows, packed, yf, ldy, w, s));
   return 0;
 }
 

@@ -37,6 +37,8 @@ struct LinProb {
   const void* Ap;      // optional input planes (hi at Ap, lo at Ap + a_lo); A may then be null
   void* Op;            // optional output planes (hi at Op, lo at Op + o_lo); O may then be null
   long long a_lo, o_lo;
+  const void* Rp;      // optional: the residual operand as planes of the output's geometry (then res is null)
+  long long r_lo;
 };
 constexpr int kMaxProb = 12;
 constexpr int kPlaneBlock = 128 * 128;                                   // bytes of one [128 x 64] bf16 block

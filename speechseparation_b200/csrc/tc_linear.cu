@@ -86,6 +86,8 @@ struct TcProb {
   const uint8_t* Al;
   uint8_t* Oh;               // output planes, or null
   uint8_t* Ol;
+  const uint8_t* Rh;         // residual operand as planes (geometry of the output), or null: fp32 rows at res
+  const uint8_t* Rl;
   int lda, ldw, ldo, ldres, ldmul;
   int M, N, K, act;
   int tile_start, tiles_m;
@@ -356,12 +358,23 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
       const bool m_vec = ((P.ldmul & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.mul) & 15) == 0);
       const bool o_vec = ((P.ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.O) & 15) == 0);
       const int ncc = (P.Oh != nullptr) ? T.bn / 32 : min(T.bn / 32, (P.N - T.n0 + 31) / 32);   // planes carry the zero padding
+      const int nch_o = (P.N + 63) >> 6;       // 64-column chunks per row block of the output (and residual) planes
+      const bool res_planes = P.Rh != nullptr && row;
       float4 pr[8], pm[8];
       auto fetch = [&](int nb) {             // residual / multiplier columns nb..nb+31 of this thread's row
+        if (res_planes) {                    // raw bf16 units: pr[0..3] hi, pr[4..7] lo (decoded where they are used)
+          const long long blk = ((long long)(T.m0 / BM) * nch_o + (nb >> 6)) * A_PLANE;
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const uint32_t off = sw128(rt, (((nb >> 5) & 1) << 2) + u);
+            pr[u] = __ldg(reinterpret_cast<const float4*>(P.Rh + blk + off));
+            pr[4 + u] = __ldg(reinterpret_cast<const float4*>(P.Rl + blk + off));
+          }
+        }
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const int n = nb + 4 * j;
-          pr[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (!res_planes) pr[j] = make_float4(0.f, 0.f, 0.f, 0.f);
           pm[j] = make_float4(1.f, 1.f, 1.f, 1.f);
           if (rrow) {
             if (r_vec && n + 3 < P.N) {
@@ -385,14 +398,13 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
           }
         }
       };
-      const bool has_rm = rrow != nullptr || mrow != nullptr;
+      const bool has_rm = rrow != nullptr || mrow != nullptr || res_planes;
       int cc = ew >> 2;
       if (has_rm && cc < ncc) fetch(T.n0 + cc * 32);
       mbar_wait(smem_u32(&bar_tfull[acc]), acc_phase);
       if (ew == BSB_TRACE_EPI && lane == 0) TRACE(2, 20);
       tc_fence_after();
       const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN_MAX);
-      const int nch_o = (P.N + 63) >> 6;       // 64-column chunks per row block of the output planes
       for (; cc < ncc; cc += CC_STEP) {
         const int nb = T.n0 + cc * 32;
         uint32_t r[32];
@@ -413,7 +425,30 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] += __uint_as_float(r[j]);
         }
-        if (has_rm) {
+        if (res_planes) {
+          auto bf2 = [](float hbits, float lbits, float& even, float& odd) {     // two bf16 pairs -> hi + lo
+            const uint32_t h = __float_as_uint(hbits), l = __float_as_uint(lbits);
+            even = __uint_as_float(h << 16) + __uint_as_float(l << 16);
+            odd = __uint_as_float(h & 0xffff0000u) + __uint_as_float(l & 0xffff0000u);
+          };
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            float e0, o0, e1, o1, e2, o2, e3, o3;
+            bf2(pr[u].x, pr[4 + u].x, e0, o0);
+            bf2(pr[u].y, pr[4 + u].y, e1, o1);
+            bf2(pr[u].z, pr[4 + u].z, e2, o2);
+            bf2(pr[u].w, pr[4 + u].w, e3, o3);
+            v[8 * u] = (v[8 * u] + e0) * pm[2 * u].x;
+            v[8 * u + 1] = (v[8 * u + 1] + o0) * pm[2 * u].y;
+            v[8 * u + 2] = (v[8 * u + 2] + e1) * pm[2 * u].z;
+            v[8 * u + 3] = (v[8 * u + 3] + o1) * pm[2 * u].w;
+            v[8 * u + 4] = (v[8 * u + 4] + e2) * pm[2 * u + 1].x;
+            v[8 * u + 5] = (v[8 * u + 5] + o2) * pm[2 * u + 1].y;
+            v[8 * u + 6] = (v[8 * u + 6] + e3) * pm[2 * u + 1].z;
+            v[8 * u + 7] = (v[8 * u + 7] + o3) * pm[2 * u + 1].w;
+          }
+          if (cc + CC_STEP < ncc) fetch(nb + CC_STEP * 32);
+        } else if (has_rm) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             v[4 * j] = (v[4 * j] + pr[j].x) * pm[j].x;
@@ -507,6 +542,8 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
     P.Al = L.Ap ? P.Ah + L.a_lo : nullptr;
     P.Oh = reinterpret_cast<uint8_t*>(L.Op);
     P.Ol = L.Op ? P.Oh + L.o_lo : nullptr;
+    P.Rh = reinterpret_cast<const uint8_t*>(L.Rp);
+    P.Rl = L.Rp ? P.Rh + L.r_lo : nullptr;
     n_planes += L.Ap != nullptr;
     P.A = L.A; P.Wh = reinterpret_cast<const __nv_bfloat16*>(L.Wh); P.Wl = reinterpret_cast<const __nv_bfloat16*>(L.Wl);
     P.bias = L.bias; P.O = L.O; P.res = L.res; P.mul = L.mul;
