@@ -12,9 +12,14 @@
 //   tensor memory : cols [0,256) gate accumulators; [256,320) h_{t-1} as bf16 hi|lo (A operand);
 //                   [320,320+KIN) x_t as bf16 hi|lo (A operand). A operands never touch smem:
 //                   the thread that owns sequence row r writes them with tcgen05.st (lane = row).
-//   warps 0-7     : epilogue; warp w owns TMEM lanes 32(w%4).. and hidden units 32(w/4)..+31 of them
+//   warps 0-7     : epilogue; warp w owns TMEM lanes 32(w%4).. and, of every 16-unit slot, units 8(w/4)..+7
 //   warp  8       : one thread issues the MMAs: 3 bf16 products per fp32 product (x = hi + lo,
 //                   hi.hi + hi.lo + lo.hi), M=128, N=256, K=16
+//
+// Only W_hh.h_{t-1} is on the serial path. The W_ih'.x_t half of step t+1 is issued while the epilogue of
+// step t is still running: the accumulator is handed back to the tensor core in four 64-column slots (16
+// hidden units each) as soon as all epilogue warps have read a slot, and the x part (N = 64 per MMA) refills
+// it; when h_t is complete only the 12 MMAs of the h part (N = 256) remain before the next epilogue.
 //
 // Gate rows are permuted to n = 4*unit + gate so a thread reads the four gates of a unit from
 // four adjacent TMEM columns, and pre-scaled by -log2(e) (i,f,o) / -2.log2(e) (g) so the
@@ -49,7 +54,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
   using C = Cfg<KIN>;
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bar_ready, bar_full;
+  __shared__ __align__(8) uint64_t bar_ready, bar_full, bar_slot[4];
   __shared__ uint32_t tmem_slot;
 
   const int tid = threadIdx.x;
@@ -63,6 +68,7 @@ lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
   if (tid == 0) {
     mbar_init(smem_u32(&bar_ready), N_EPI_WARPS * 32);
     mbar_init(smem_u32(&bar_full), 1);
+    for (int i = 0; i < 4; ++i) mbar_init(smem_u32(&bar_slot[i]), N_EPI_WARPS * 32);
     fence_mbar_init();
   }
   if (warp == N_EPI_WARPS) {
@@ -90,7 +96,7 @@ lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
     const bool valid = seq < a.nseq;
     const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16);
     const float* xrow = a.x + seq * a.x_seq + hf * C::XH;
-    float* hrow = a.hout + seq * a.h_seq + dir * kFeat + hf * 32;
+    float* hrow = a.hout + seq * a.h_seq + dir * kFeat + hf * 8;
 
     float xr[C::XH];
     auto load_x = [&](int step) {
@@ -122,10 +128,13 @@ lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
 #pragma unroll
     for (int i = 0; i < 32; ++i) c[i] = 0.f;
 
+    // round 0: x of the first step; nothing to wait for, h_{-1} = 0
     load_x(reverse ? a.nsteps - 1 : 0);
     store_x();
     tmem_st_wait();
     tc_fence_before();
+#pragma unroll
+    for (int sl = 0; sl < 4; ++sl) mbar_arrive(smem_u32(&bar_slot[sl]));
     mbar_arrive(smem_u32(&bar_ready));
 
     for (int it = 0; it < a.nsteps; ++it) {
@@ -134,16 +143,24 @@ lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
       if (more) load_x(reverse ? step - 1 : step + 1);       // in flight while the MMAs run
       mbar_wait(smem_u32(&bar_full), it & 1);
       tc_fence_after();
+      if (more) {                                            // all MMAs of this step are done: the x columns are free
+        store_x();
+        tmem_st_wait();
+      }
       float* hdst = hrow + (long long)step * a.h_step;
 #pragma unroll
-      for (int ch = 0; ch < 4; ++ch) {                       // 8 units = 32 accumulator columns
+      for (int sl = 0; sl < 4; ++sl) {                       // slot = 16 units = 64 accumulator columns; 8 units here
         uint32_t r[32];
-        tmem_ld_32x32(tlane + COL_ACC + hf * 128 + ch * 32, r);
-        tmem_ld_wait();
+        tmem_ld_32x32(tlane + COL_ACC + sl * 64 + hf * 32, r);
+        tmem_ld_wait32(r);
+        if (more) {                                          // this thread is done with the slot (and x_{t+1} is in place)
+          tc_fence_before();
+          mbar_arrive(smem_u32(&bar_slot[sl]));
+        }
         float h[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          const float4 b = *reinterpret_cast<const float4*>(bias_s + hf * 128 + ch * 32 + j * 4);
+          const float4 b = *reinterpret_cast<const float4*>(bias_s + sl * 64 + hf * 32 + j * 4);
           const float ti = fminf(__uint_as_float(r[4 * j + 0]) + b.x, kClamp);
           const float tf = fminf(__uint_as_float(r[4 * j + 1]) + b.y, kClamp);
           const float tg = fminf(__uint_as_float(r[4 * j + 2]) + b.z, kClamp);
@@ -151,27 +168,26 @@ lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
           const float ei = ex2_approx(ti), ef = ex2_approx(tf), eg = ex2_approx(tg), eo = ex2_approx(to);
           const float pi = 1.f + ei, pf = 1.f + ef, pg = 1.f + eg;
           const float pig = pi * pg;
-          const float num = fmaf(c[ch * 8 + j], pig, (1.f - eg) * pf);
+          const float num = fmaf(c[sl * 8 + j], pig, (1.f - eg) * pf);
           const float cn = num * rcp_approx(pf * pig);
-          c[ch * 8 + j] = cn;
+          c[sl * 8 + j] = cn;
           const float ec = ex2_approx(fminf(cn * -2.885390081777927f, kClamp));
           h[j] = (1.f - ec) * rcp_approx((1.f + eo) * (1.f + ec));
         }
         if (valid) {
-          *reinterpret_cast<float4*>(hdst + ch * 8) = make_float4(h[0], h[1], h[2], h[3]);
-          *reinterpret_cast<float4*>(hdst + ch * 8 + 4) = make_float4(h[4], h[5], h[6], h[7]);
+          *reinterpret_cast<float4*>(hdst + sl * 16) = make_float4(h[0], h[1], h[2], h[3]);
+          *reinterpret_cast<float4*>(hdst + sl * 16 + 4) = make_float4(h[4], h[5], h[6], h[7]);
         }
         if (more) {
           uint32_t hi[4], lo[4];
 #pragma unroll
           for (int i = 0; i < 4; ++i) split2(h[2 * i], h[2 * i + 1], hi[i], lo[i]);
-          const uint32_t col = COL_AH + hf * 16 + ch * 4;
+          const uint32_t col = COL_AH + sl * 8 + hf * 4;     // unit 16 sl + 8 hf + 2 i -> 32-bit column unit / 2
           tmem_st_32x4(tlane + col, hi);
           tmem_st_32x4(tlane + col + 32, lo);
         }
       }
       if (more) {
-        store_x();
         tmem_st_wait();
         tc_fence_before();
         mbar_arrive(smem_u32(&bar_ready));
@@ -179,27 +195,52 @@ lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
     }
   } else {
     // ================= MMA issuer =================
-    const uint32_t idesc = make_idesc_bf16(TILE, kGates);
+    const uint32_t idesc_slot = make_idesc_bf16(TILE, 64);
+    const uint32_t idesc_full = make_idesc_bf16(TILE, kGates);
     const uint32_t d_tmem = tmem_base + COL_ACC;
+    constexpr int NCX = C::NCH - 1;                          // K chunks of the x part
     for (int it = 0; it < a.nsteps; ++it) {
-      mbar_wait(smem_u32(&bar_ready), it & 1);
+      const uint32_t par = it & 1;
+      // x part of this step, slot by slot as the epilogue of the previous step releases the accumulator
+      for (int sl = 0; sl < 4; ++sl) {
+        mbar_wait(smem_u32(&bar_slot[sl]), par);
+        tc_fence_after();
+        if (lane == 0) {
+          uint32_t accumulate = 0;
+#pragma unroll
+          for (int ch = 0; ch < NCX; ++ch) {
+            const uint32_t a_hi0 = tmem_base + COL_AX + ch * 32;
+            const uint32_t a_lo0 = a_hi0 + KIN / 2;
+            // rows 64 sl .. 64 sl + 63 of the weight chunk: 8 swizzle atoms of 8 rows x 128 B further
+            const uint64_t w_hi = make_sw128_desc(smem_base + ch * CHUNK_BYTES + sl * 64 * 128);
+            const uint64_t w_lo = make_sw128_desc(smem_base + C::PLANE + ch * CHUNK_BYTES + sl * 64 * 128);
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+              const uint64_t adv = (uint64_t)(kk * 32 >> 4);   // 16 bf16 = 32 bytes along K
+              mma_bf16_ts(d_tmem + sl * 64, a_lo0 + kk * 8, w_hi + adv, idesc_slot, accumulate);   // small terms first
+              mma_bf16_ts(d_tmem + sl * 64, a_hi0 + kk * 8, w_lo + adv, idesc_slot, 1);
+              mma_bf16_ts(d_tmem + sl * 64, a_hi0 + kk * 8, w_hi + adv, idesc_slot, 1);
+              accumulate = 1;
+            }
+          }
+        }
+        __syncwarp();
+      }
+      // h part: needs every unit of h_{t-1}
+      mbar_wait(smem_u32(&bar_ready), par);
       tc_fence_after();
       if (lane == 0) {
-        uint32_t accumulate = 0;
-        const int nch = it == 0 ? C::NCH - 1 : C::NCH;       // h_{-1} = 0: skip the W_hh chunk
-        for (int ch = 0; ch < nch; ++ch) {
-          const bool hpart = ch == C::NCH - 1;
-          const uint32_t a_hi0 = tmem_base + (hpart ? COL_AH : COL_AX + ch * 32);
-          const uint32_t a_lo0 = a_hi0 + (hpart ? 32 : KIN / 2);
-          const uint64_t w_hi = make_sw128_desc(smem_base + ch * CHUNK_BYTES);
-          const uint64_t w_lo = make_sw128_desc(smem_base + C::PLANE + ch * CHUNK_BYTES);
+        if (it > 0) {                                        // h_{-1} = 0
+          const uint32_t a_hi0 = tmem_base + COL_AH;
+          const uint32_t a_lo0 = a_hi0 + 32;
+          const uint64_t w_hi = make_sw128_desc(smem_base + NCX * CHUNK_BYTES);
+          const uint64_t w_lo = make_sw128_desc(smem_base + C::PLANE + NCX * CHUNK_BYTES);
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {
-            const uint64_t adv = (uint64_t)(kk * 32 >> 4);   // 16 bf16 = 32 bytes along K
-            mma_bf16_ts(d_tmem, a_lo0 + kk * 8, w_hi + adv, idesc, accumulate);   // small terms first
-            mma_bf16_ts(d_tmem, a_hi0 + kk * 8, w_lo + adv, idesc, 1);
-            mma_bf16_ts(d_tmem, a_hi0 + kk * 8, w_hi + adv, idesc, 1);
-            accumulate = 1;
+            const uint64_t adv = (uint64_t)(kk * 32 >> 4);
+            mma_bf16_ts(d_tmem, a_lo0 + kk * 8, w_hi + adv, idesc_full, 1);
+            mma_bf16_ts(d_tmem, a_hi0 + kk * 8, w_lo + adv, idesc_full, 1);
+            mma_bf16_ts(d_tmem, a_hi0 + kk * 8, w_hi + adv, idesc_full, 1);
           }
         }
         mma_commit(smem_u32(&bar_full));

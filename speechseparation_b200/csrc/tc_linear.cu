@@ -70,7 +70,7 @@ template <bool A_PLANES> struct Roles {
 };
 template <bool A_PLANES> constexpr int smem_bytes() { return STAGES * STAGE_BYTES + 1024; }   // + alignment slack
 constexpr int N_PRODUCERS = N_GROUP_WARPS * 32;               // 256 threads fill one stage
-constexpr int REGS_PRODUCER = 72, REGS_CONTROL = 40, REGS_EPILOGUE = 152;   // released 512*8 + 128*40 = taken 128*72
+constexpr int REGS_PRODUCER = 64, REGS_CONTROL = 40, REGS_EPILOGUE = 184;   // released 512*16 + 128*40 = taken 128*104
 static_assert(STAGES == 2, "one producer group per stage");
 constexpr int TMEM_COLS = 512;       // 2 accumulators x 256 fp32 columns
 
