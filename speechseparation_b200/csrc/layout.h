@@ -60,7 +60,9 @@ struct RnnBlock {
   long long sqw[2];
   long long sqb[2];
 };
-constexpr long long kSeqImgFloats = 16 * 8 * 2 * 32 * 4;
+constexpr long long kSeqFragFloats = 16 * 8 * 2 * 32 * 4;         // mma.sync A fragments of [W_ih' | W_hh]
+constexpr long long kSeqXImgFloats = 2 * kGates * 64 * 2 / 4;      // W_ih' again as tcgen05 B operand: bf16 hi/lo [256][64], SWIZZLE_128B
+constexpr long long kSeqImgFloats = kSeqFragFloats + kSeqXImgFloats;
 inline constexpr int tc_lstm_kin(int layer, int ndir) { return layer == 0 ? kFeat : kFeat * ndir; }
 inline constexpr int tc_lstm_chunks(int layer, int ndir) { return (tc_lstm_kin(layer, ndir) + kFeat) / 64; }
 inline constexpr long long tc_lstm_img_floats(int layer, int ndir) {   // 2 planes x chunks x 256 x 64 bf16
