@@ -251,7 +251,7 @@ def test_tensor_core_linears_match_fp32_kernels(dev, model, oracle_sd):
     from speechseparation_b200 import _lib
     l = _lib.lib()
     packed = model.packed_weights(dev)
-    for C, T in [(1, 128), (3, 131), (2, 300)]:
+    for C, T in [(1, 128), (3, 131), (2, 300), (1, 257)]:
         rs = np.random.RandomState(C * 1000 + T)
         x = torch.from_numpy((rs.standard_normal((C, 2050, T)) * 2.0).astype(np.float32))
         R = C * T
@@ -317,10 +317,12 @@ def test_band_axis_tensor_core_lstm_vs_oracle(dev, model, oracle_sd, C, T):
         assert not torch.equal(got, fp32)          # really a different kernel
 
 
-@pytest.mark.parametrize("C,T,with_state", [(1, 2, False), (1, 3, True), (2, 37, True), (3, 130, False), (5, 64, True)])
+@pytest.mark.parametrize("C,T,with_state", [(1, 2, False), (1, 3, True), (2, 37, True), (3, 130, False), (5, 64, True),
+                                             (1, 15, True), (1, 16, False), (2, 17, True), (1, 33, False), (2, 100, True)])
 def test_time_axis_lstm_vs_oracle_with_state(dev, model, oracle_sd, C, T, with_state):
     """TimewiseLSTM blocks (bsrnn.py:101-128) on the 8-sequences-per-CTA kernel: ragged last CTA
-    (12, 24, 36, 60 sequences), initial (h, c) in, final (h, c) out, against the ATen LSTM."""
+    (12, 24, 36, 60 sequences), step counts around the 4-step ring quarters and 16-step tcgen05 blocks of the
+    input projection, initial (h, c) in, final (h, c) out, against the ATen LSTM."""
     from speechseparation_b200 import _lib
     l = _lib.lib()
     packed = model.packed_weights(dev)
