@@ -159,10 +159,11 @@ inline void res_planes(LinProb& P, const BandPlanes& b, int i) { P.Rp = b.band[i
 inline bool use_planes(long long rows) { return rows >= kTcMinRows && !force_ffma(); }
 
 int single_linear(const void* packed, const Lin& l, const float* A, int lda, float* O, int ldo, long long M, int act,
-                  const float* res, int ldres, cudaStream_t s) {
+                  const float* res, int ldres, cudaStream_t s, const void* a_planes = nullptr, long long a_lo = 0) {
   GroupedArgs g{};
   g.nprob = 1;
   set_prob(g.p[0], packed, l, A, lda, O, ldo, (int)M, act, res, ldres);
+  if (a_planes != nullptr) { g.p[0].Ap = a_planes; g.p[0].a_lo = a_lo; g.p[0].A = nullptr; }
   CK(launch_grouped_linear(g, s));
   return 0;
 }
@@ -371,11 +372,12 @@ int run_rnn_block(int j, const float* fin, int C, int T, const void* packed, con
       a.h_step = ldh; a.h_seq = (long long)kBands * ldh;
       for (int d = 0; d < R.ndir; ++d) { a.wimg[d] = PW(packed, R.tcw[layer][d]); a.bias[d] = PW(packed, R.tcb[layer][d]); }
       a.nseq = C * T; a.nsteps = kBands; a.ndir = R.ndir;
+      if (layer == 1) { a.hplanes = w.planeA; a.hp_lo = w.plane_lo; }   // the fc below takes its A operand as planes
       CK(launch_lstm_tc(a, s));
       std::snprintf(nm, sizeof(nm), "rnn%d.rec%d", j, layer);
       mark(nm, s);
     }
-    CKI(single_linear(packed, R.fc, hl[1], ldh, fout, kFeat, rows, ACT_NONE, fin, kFeat, s));
+    CKI(single_linear(packed, R.fc, hl[1], ldh, fout, kFeat, rows, ACT_NONE, fin, kFeat, s, w.planeA, w.plane_lo));
     std::snprintf(nm, sizeof(nm), "rnn%d.fc", j);
     mark(nm, s);
     return 0;
@@ -396,11 +398,16 @@ int run_rnn_block(int j, const float* fin, int C, int T, const void* packed, con
       const long long per = (long long)a.nseq * kFeat;       // state [2(h,c)][2 layers][nseq][64]
       if (st_in) { a.h0 = st_in + layer * per; a.c0 = st_in + (2 + layer) * per; }
       if (st_out) { a.hN = st_out + layer * per; a.cN = st_out + (2 + layer) * per; }
+      const bool planes = layer == 1 && rows >= kTcMinRows;           // the fc below runs on the tensor-core kernel
+      if (planes) { a.hplanes = w.planeA; a.hp_lo = w.plane_lo; }
       CK(launch_lstm_seq(a, s));
       std::snprintf(nm, sizeof(nm), "rnn%d.rec%d", j, layer);
       mark(nm, s);
     }
-    CKI(single_linear(packed, R.fc, hl[1], ldh, fout, kFeat, rows, ACT_NONE, fin, kFeat, s));
+    if (rows >= kTcMinRows)
+      CKI(single_linear(packed, R.fc, hl[1], ldh, fout, kFeat, rows, ACT_NONE, fin, kFeat, s, w.planeA, w.plane_lo));
+    else
+      CKI(single_linear(packed, R.fc, hl[1], ldh, fout, kFeat, rows, ACT_NONE, fin, kFeat, s));
     std::snprintf(nm, sizeof(nm), "rnn%d.fc", j);
     mark(nm, s);
     return 0;

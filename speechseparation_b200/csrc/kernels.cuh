@@ -89,6 +89,10 @@ struct LstmTcArgs {
   const float* bias[2];      // per direction: RnnBlock::tcb
   long long x_seq, x_step, h_seq, h_step;
   int nseq, nsteps, ndir, kin;
+  // optional: h goes out as bf16 hi/lo planes (LinProb::Ap geometry, row = seq * nsteps + step, 64-column chunk =
+  // direction) for the Linear that follows, instead of fp32 rows at hout
+  void* hplanes;
+  long long hp_lo;
 };
 cudaError_t launch_lstm_tc(const LstmTcArgs& a, cudaStream_t s);
 // Time-axis LSTM layer with the input projection fused, 8 sequences per CTA on mma.sync (lstm_seq.cu).
@@ -104,6 +108,10 @@ struct LstmSeqArgs {
   float* cN;
   long long x_outer, x_inner, x_step, h_outer, h_inner, h_step;
   int n_inner, nseq, nsteps;
+  // optional: h goes out as bf16 hi/lo planes (LinProb::Ap geometry, one 64-column chunk, row = h offset / 64)
+  // for the Linear that follows, instead of fp32 rows at hout
+  void* hplanes;
+  long long hp_lo;
 };
 cudaError_t launch_lstm_seq(const LstmSeqArgs& a, cudaStream_t s);
 constexpr int kLstmSeqMinSteps = 2;  // single steps (streaming hops) stay on the FFMA recurrence

@@ -156,7 +156,9 @@ lstm_seq_kernel(const __grid_constant__ LstmSeqArgs a) {
     const int lg = seq0 + lseq;
     const bool lvalid = io && lg < a.nseq;
     float* hptr = a.hout;
-    if (lvalid) hptr += (long long)(lg / a.n_inner) * a.h_outer + (long long)(lg % a.n_inner) * a.h_inner + part * 4;
+    long long hoff = 0;          // float offset of (sequence, step 0) in the output rows
+    if (lvalid) hoff = (long long)(lg / a.n_inner) * a.h_outer + (long long)(lg % a.n_inner) * a.h_inner;
+    hptr += hoff + part * 4;
 
     // W_ih'.x_t of this lane's four accumulator positions: ring[half][step % 4][column][sequence]
     const uint8_t* ring = smem_gen + OFF_RING + (w * 16 + gr) * (SQ * 4) + tq * 8;
@@ -204,8 +206,20 @@ lstm_seq_kernel(const __grid_constant__ LstmSeqArgs a) {
         fetch_x(t + 1);
       }
       bar_recurrence();
-      if (lvalid)
-        *reinterpret_cast<float4*>(hptr + (long long)t * a.h_step) = *reinterpret_cast<const float4*>(&hF[nxt][lseq][part * 4]);
+      if (lvalid) {
+        if (a.hplanes != nullptr) {
+          // A operand of the Linear that follows: row = output row index, one 64-column chunk; the bf16 hi/lo
+          // pairs are already in the B-fragment buffers
+          const long long m = (hoff + (long long)t * a.h_step) >> 6;
+          const int r = (int)(m & 127);
+          uint8_t* p = reinterpret_cast<uint8_t*>(a.hplanes) + (m >> 7) * (128 * 128) + r * 128 + (((part >> 1) ^ (r & 7)) << 4) +
+                       (part & 1) * 8;
+          *reinterpret_cast<uint2*>(p) = *reinterpret_cast<const uint2*>(&hB[nxt][0][lseq][part * 4]);
+          *reinterpret_cast<uint2*>(p + a.hp_lo) = *reinterpret_cast<const uint2*>(&hB[nxt][1][lseq][part * 4]);
+        } else {
+          *reinterpret_cast<float4*>(hptr + (long long)t * a.h_step) = *reinterpret_cast<const float4*>(&hF[nxt][lseq][part * 4]);
+        }
+      }
     }
   } else if (w < MMA_WARP) {
     // ================= helpers: x rows -> A operand, accumulator -> ring =================

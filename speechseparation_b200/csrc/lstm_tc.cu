@@ -174,14 +174,25 @@ lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
           const float ec = ex2_approx(fminf(cn * -2.885390081777927f, kClamp));
           h[j] = (1.f - ec) * rcp_approx((1.f + eo) * (1.f + ec));
         }
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) split2(h[2 * i], h[2 * i + 1], hi[i], lo[i]);
         if (valid) {
-          *reinterpret_cast<float4*>(hdst + sl * 16) = make_float4(h[0], h[1], h[2], h[3]);
-          *reinterpret_cast<float4*>(hdst + sl * 16 + 4) = make_float4(h[4], h[5], h[6], h[7]);
+          if (a.hplanes != nullptr) {
+            // A operand of the Linear that follows: row seq*nsteps + step, 64-column chunk = direction, units
+            // 16 sl + 8 hf .. +7 = 16-byte unit 2 sl + hf of the 128-byte row
+            const long long m = seq * a.nsteps + step;
+            const int r = (int)(m & 127);
+            uint8_t* p = reinterpret_cast<uint8_t*>(a.hplanes) + ((m >> 7) * a.ndir + dir) * (128 * 128) + r * 128 +
+                         (((2 * sl + hf) ^ (r & 7)) << 4);
+            *reinterpret_cast<uint4*>(p) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4*>(p + a.hp_lo) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+          } else {
+            *reinterpret_cast<float4*>(hdst + sl * 16) = make_float4(h[0], h[1], h[2], h[3]);
+            *reinterpret_cast<float4*>(hdst + sl * 16 + 4) = make_float4(h[4], h[5], h[6], h[7]);
+          }
         }
         if (more) {
-          uint32_t hi[4], lo[4];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) split2(h[2 * i], h[2 * i + 1], hi[i], lo[i]);
           const uint32_t col = COL_AH + sl * 8 + hf * 4;     // unit 16 sl + 8 hf + 2 i -> 32-bit column unit / 2
           tmem_st_32x4(tlane + col, hi);
           tmem_st_32x4(tlane + col + 32, lo);
