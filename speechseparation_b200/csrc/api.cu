@@ -66,8 +66,8 @@ struct Ws {
   long long plane_lo;   // byte distance hi -> lo plane inside a buffer
   long long mtiles;     // 128-row tiles
 };
-// widest layer output in 64-column chunks summed over the 11 bands (bandFCs_back.2: 7 x 2 + 3 + 6 + 12 + 9 = 44)
-constexpr int kPlaneChunksMax = 44;
+// widest layer output in 32-column chunks summed over the 11 bands (bandFCs_back.2: 7 x 4 + 6 + 12 + 24 + 17 = 87)
+constexpr int kPlaneChunksMax = 88;
 
 inline size_t rup256(size_t v) { return (v + 255) / 256 * 256; }
 

@@ -32,8 +32,8 @@ struct LinProb {
   int tiles_n;
   // Tensor-core path only: activations that go from one Linear straight into the next never exist as fp32
   // rows. The producing epilogue writes them as "planes": bf16 hi and lo (x = hi + lo), blocked as
-  // [m-tile of 128 rows][k-chunk of 64 columns][128 rows x 128 B, SWIZZLE_128B] = the shared-memory image the
-  // consuming layer's tcgen05.mma reads, so its A operand is two 16 KB bulk copies per chunk (plane_blocks()).
+  // [m-tile of 128 rows][k-chunk of 32 columns][128 rows x 64 B, SWIZZLE_64B] = the shared-memory image the
+  // consuming layer's tcgen05.mma reads, so its A operand is two 8 KB bulk copies per chunk.
   const void* Ap;      // optional input planes (hi at Ap, lo at Ap + a_lo); A may then be null
   void* Op;            // optional output planes (hi at Op, lo at Op + o_lo); O may then be null
   long long a_lo, o_lo;
@@ -41,8 +41,12 @@ struct LinProb {
   long long r_lo;
 };
 constexpr int kMaxProb = 12;
-constexpr int kPlaneBlock = 128 * 128;                                   // bytes of one [128 x 64] bf16 block
-inline int plane_chunks(int n) { return (n + 63) / 64; }
+constexpr int kPlaneK = 32;                                              // columns per plane block = K chunk of the GEMM
+constexpr int kPlaneBlock = 128 * kPlaneK * 2;                           // bytes of one [128 x 32] bf16 block
+inline int plane_chunks(int n) { return (n + kPlaneK - 1) / kPlaneK; }
+// byte offset of 16-byte unit `c` (0..3) of row `r` in a K-major SWIZZLE_64B image (rows of 64 B; verified on the
+// device by tools/sw64_probe.cu: layout code 4, unit ^= (row >> 1) & 3, 8-row groups 512 B apart)
+__host__ __device__ inline unsigned sw64(int r, int c) { return (unsigned)(r * 64 + ((c ^ ((r >> 1) & 3)) << 4)); }
 struct GroupedArgs {
   LinProb p[kMaxProb];
   int nprob;

@@ -208,11 +208,11 @@ lstm_seq_kernel(const __grid_constant__ LstmSeqArgs a) {
       bar_recurrence();
       if (lvalid) {
         if (a.hplanes != nullptr) {
-          // A operand of the Linear that follows: row = output row index, one 64-column chunk; the bf16 hi/lo
-          // pairs are already in the B-fragment buffers
+          // A operand of the Linear that follows (kernels.cuh planes: [m-tile][32-column chunk][128 x 64 B]): row =
+          // output row index, columns 4 part .. +3; the bf16 hi/lo pairs are already in the B-fragment buffers
           const long long m = (hoff + (long long)t * a.h_step) >> 6;
           const int r = (int)(m & 127);
-          uint8_t* p = reinterpret_cast<uint8_t*>(a.hplanes) + (m >> 7) * (128 * 128) + r * 128 + (((part >> 1) ^ (r & 7)) << 4) +
+          uint8_t* p = reinterpret_cast<uint8_t*>(a.hplanes) + ((m >> 7) * 2 + (part >> 3)) * kPlaneBlock + sw64(r, (part & 7) >> 1) +
                        (part & 1) * 8;
           *reinterpret_cast<uint2*>(p) = *reinterpret_cast<const uint2*>(&hB[nxt][0][lseq][part * 4]);
           *reinterpret_cast<uint2*>(p + a.hp_lo) = *reinterpret_cast<const uint2*>(&hB[nxt][1][lseq][part * 4]);

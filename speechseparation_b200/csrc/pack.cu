@@ -22,15 +22,15 @@ __global__ void pack_bias_kernel(const float* __restrict__ b1, const float* __re
 }
 
 // W [N][K] fp32 -> bf16 hi/lo planes in the tensor-core kernel's shared-memory image: the plane is cut
-// into blocks of (up to) 256 rows x 64 k, each stored contiguously as [rows][128 B] with the
-// 16-byte chunks of a row XOR-swizzled by (row & 7) (UMMA SWIZZLE_128B, K-major), blocks ordered
+// into blocks of (up to) 256 rows x 32 k, each stored contiguously as [rows][64 B] with the
+// 16-byte units of a row XOR-swizzled by (row >> 1) & 3 (UMMA SWIZZLE_64B, K-major), blocks ordered
 // n-tile major, k-chunk minor, so tc_linear.cu fetches a block with one cp.async.bulk.
 // ldd = K padded to 64; rows are padded to 64 (zeros come from the memset of the packed buffer).
 __global__ void pack_split_kernel(const float* __restrict__ src, int N, int K, uint8_t* __restrict__ hi,
                                   uint8_t* __restrict__ lo, int ldd) {
   const long long total = (long long)N * K;
   const int npad = (N + 63) / 64 * 64;
-  const int nch = ldd >> 6;
+  const int nch = ldd >> 5;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const int n = (int)(i / K), k = (int)(i - (long long)n * K);
@@ -39,8 +39,8 @@ __global__ void pack_split_kernel(const float* __restrict__ src, int N, int K, u
     const __nv_bfloat16 l = __float2bfloat16_rn(w - __bfloat162float(h));
     const int n0 = n & ~255, r = n & 255;
     const int bn = min(256, npad - n0);
-    const int c = k >> 6, kk = k & 63;
-    const size_t off = ((size_t)n0 * nch + (size_t)c * bn + r) * 128 + (((kk >> 3) ^ (r & 7)) << 4) + (kk & 7) * 2;
+    const int c = k >> 5, kk = k & 31;
+    const size_t off = ((size_t)n0 * nch + (size_t)c * bn) * 64 + sw64(r, kk >> 3) + (kk & 7) * 2;
     *reinterpret_cast<__nv_bfloat16*>(hi + off) = h;
     *reinterpret_cast<__nv_bfloat16*>(lo + off) = l;
   }

@@ -42,12 +42,12 @@ namespace {
 using namespace ptx;
 
 constexpr int BM = 128;              // rows per tile (UMMA M)
-constexpr int BK = 64;               // bf16 elements per K chunk = one 128-byte swizzle row
+constexpr int BK = kPlaneK;          // bf16 elements per K chunk = one 64-byte swizzle row (two k16 MMA steps)
 constexpr int BN_MAX = 256;          // columns per tile (UMMA N <= 256)
-constexpr int STAGES = 2;
-constexpr int A_PLANE = BM * 128;            // bytes of one A plane per stage (16 KB)
-constexpr int W_PLANE = BN_MAX * 128;        // bytes of one W plane per stage (32 KB)
-constexpr int STAGE_BYTES = 2 * A_PLANE + 2 * W_PLANE;   // 96 KB
+constexpr int STAGES = 4;
+constexpr int A_PLANE = BM * BK * 2;         // bytes of one A plane per stage (8 KB) = kPlaneBlock
+constexpr int W_PLANE = BN_MAX * BK * 2;     // bytes of one W plane per stage (16 KB)
+constexpr int STAGE_BYTES = 2 * A_PLANE + 2 * W_PLANE;   // 48 KB
 // Warp roles (setmaxnreg works per warpgroup = 4 consecutive warps):
 //   fp32-row A (A_PLANES = false), 24 warps at 80 registers:
 //     warps 0-7   A producer group 0 (fills stage 0)      warps 8-15  A producer group 1 (fills stage 1)
@@ -71,7 +71,7 @@ template <bool A_PLANES> struct Roles {
 template <bool A_PLANES> constexpr int smem_bytes() { return STAGES * STAGE_BYTES + 1024; }   // + alignment slack
 constexpr int N_PRODUCERS = N_GROUP_WARPS * 32;               // 256 threads fill one stage
 constexpr int REGS_PRODUCER = 64, REGS_CONTROL = 40, REGS_EPILOGUE = 184;   // released 512*16 + 128*40 = taken 128*104
-static_assert(STAGES == 2, "one producer group per stage");
+static_assert(STAGES == 4 && A_PLANE == kPlaneBlock, "two producer groups alternate over four stages");
 constexpr int TMEM_COLS = 512;       // 2 accumulators x 256 fp32 columns
 
 struct TcProb {
@@ -118,20 +118,28 @@ __device__ __forceinline__ Tile decode_tile(const TcArgs& args, int tile) {
   return t;
 }
 
-// byte offset of 16-byte chunk `c` (0..7) of row `r` inside a 128B-swizzled K-major plane
-__device__ __forceinline__ uint32_t sw128(int r, int c) { return (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4)); }
+// K-major SWIZZLE_64B operand descriptor: rows of 64 B, 8-row groups 512 B apart (kernels.cuh sw64)
+__device__ __forceinline__ uint64_t make_sw64_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(512 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)4 << 61;
+  return d;
+}
 
-// ---- A producer: 128 rows x 64 k of fp32 -> hi/lo bf16 planes --------------------------------
-// 256 threads; thread t owns the float4 units u = t + 256 i (row u/16, floats 4(u%16)..+3), i < 8, so
-// every warp-level load covers 512 consecutive bytes (2 rows x 256 B): full sectors per request.
-struct AChunk { float4 v[8]; };
+// ---- A producer: 128 rows x 32 k of fp32 -> hi/lo bf16 planes --------------------------------
+// 256 threads; thread t owns the float4 units u = t + 256 i (row u/8, floats 4(u%8)..+3), i < 4, so
+// every warp-level load covers 4 rows x 128 consecutive bytes.
+struct AChunk { float4 v[4]; };
 
 __device__ __forceinline__ void load_a(const TcProb& P, int m0, int k0, int t, AChunk& a) {
   const bool vec = ((P.lda & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.A) & 15) == 0);
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
+  for (int i = 0; i < 4; ++i) {
     const int u = t + 256 * i;
-    const int r = u >> 4, c = u & 15;
+    const int r = u >> 3, c = u & 7;
     const int m = m0 + r, k = k0 + c * 4;
     float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
     if (m < P.M && k < P.K) {
@@ -151,13 +159,13 @@ __device__ __forceinline__ void load_a(const TcProb& P, int m0, int k0, int t, A
 
 __device__ __forceinline__ void store_a(const AChunk& a, uint8_t* a_hi, uint8_t* a_lo, int t) {
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
+  for (int i = 0; i < 4; ++i) {
     const int u = t + 256 * i;
-    const int r = u >> 4, c = u & 15;
+    const int r = u >> 3, c = u & 7;
     uint2 h, l;
     split2(a.v[i].x, a.v[i].y, h.x, l.x);
     split2(a.v[i].z, a.v[i].w, h.y, l.y);
-    const uint32_t off = sw128(r, c >> 1) + (c & 1) * 8;     // half of a 16-byte swizzle chunk
+    const uint32_t off = sw64(r, c >> 1) + (c & 1) * 8;      // half of a 16-byte swizzle unit
     *reinterpret_cast<uint2*>(a_hi + off) = h;
     *reinterpret_cast<uint2*>(a_lo + off) = l;
   }
@@ -226,12 +234,11 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
   TRACE_DECL;
 
   if (warp < R::PROD_WARPS) {
-    // ================= A producers: group g owns stage g = every second K chunk of the CTA's chunk stream ====
+    // ================= A producers: group g fills stages 2g and 2g+1 = chunks 4j+2g, 4j+2g+1 of the CTA's stream ====
+    // (two chunks = eight 16-byte loads per thread are requested before the first is converted)
     setmaxnreg_dec<REGS_PRODUCER>();
     const int grp = warp / N_GROUP_WARPS;
     const int pt = (warp % N_GROUP_WARPS) * 32 + lane;      // thread 0..255 of the group
-    const uint32_t full = smem_u32(&bar_full[grp]), empty = smem_u32(&bar_empty[grp]);
-    uint8_t* sb = smem_gen + grp * STAGE_BYTES;
     int tile = blockIdx.x, kc = 0, nk = 0;
     Tile T{};
     auto open_tile = [&]() {
@@ -241,25 +248,33 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
       }
     };
     auto next_chunk = [&]() {
-      if (++kc == nk) { kc = 0; tile += gridDim.x; open_tile(); }
+      if (tile < args.total_tiles && ++kc == nk) { kc = 0; tile += gridDim.x; open_tile(); }
     };
     open_tile();
-    if (grp == 1 && tile < args.total_tiles) next_chunk();
+    if (grp == 1) { next_chunk(); next_chunk(); }
     uint32_t phase = 0;
-    AChunk regs;
-    if (tile < args.total_tiles) load_a(args.p[T.pi], T.m0, kc * BK, pt, regs);
     while (tile < args.total_tiles) {
-      mbar_wait(empty, phase ^ 1);
-      if (pt == 0) TRACE(grp ? 3 : 0, 1 + 100 * grp);
-      store_a(regs, sb, sb + A_PLANE, pt);
-      fence_proxy_async_smem();
-      mbar_arrive(full);
-      if (pt == 0) TRACE(grp ? 3 : 0, 3 + 100 * grp);
-      phase ^= 1;
+      AChunk r0, r1;
+      load_a(args.p[T.pi], T.m0, kc * BK, pt, r0);
       next_chunk();
-      if (tile < args.total_tiles) next_chunk();
-      if (tile < args.total_tiles) load_a(args.p[T.pi], T.m0, kc * BK, pt, regs);
-      if (pt == 0) TRACE(grp ? 3 : 0, 4 + 100 * grp);
+      const bool second = tile < args.total_tiles;
+      if (second) load_a(args.p[T.pi], T.m0, kc * BK, pt, r1);
+      next_chunk();
+      next_chunk();
+      next_chunk();
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        if (h == 1 && !second) break;
+        const int stage = 2 * grp + h;
+        uint8_t* sb = smem_gen + stage * STAGE_BYTES;
+        mbar_wait(smem_u32(&bar_empty[stage]), phase ^ 1);
+        if (pt == 0) TRACE(grp ? 3 : 0, 1 + 100 * grp);
+        store_a(h == 0 ? r0 : r1, sb, sb + A_PLANE, pt);
+        fence_proxy_async_smem();
+        mbar_arrive(smem_u32(&bar_full[stage]));
+        if (pt == 0) TRACE(grp ? 3 : 0, 3 + 100 * grp);
+      }
+      phase ^= 1;
     }
   } else if (warp < EPI_WARP0) {
     if (!A_PLANES) setmaxnreg_dec<REGS_CONTROL>();
@@ -275,8 +290,8 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
           mbar_wait(smem_u32(&bar_empty[stage]), phase ^ 1);
           TRACE(4, 30 + stage);
           // W blocks [bn x 64] bf16, already swizzled: (n0 * nch + kc * bn) * 128 bytes into each plane
-          const uint32_t bytes = (uint32_t)T.bn * 128u;
-          const long long off = ((long long)T.n0 * (P.ldw >> 6) + (long long)kc * T.bn) * 128;
+          const uint32_t bytes = (uint32_t)T.bn * (BK * 2);
+          const long long off = ((long long)T.n0 * (P.ldw >> 5) + (long long)kc * T.bn) * (BK * 2);
           const uint32_t bar = smem_u32(&bar_full[stage]);
           mbar_arrive_expect_tx(bar, 2 * bytes + (A_PLANES ? 2 * A_PLANE : 0));
           if (A_PLANES) {
@@ -308,10 +323,10 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
         tc_fence_after();
         if (lane == 0) {
           const uint32_t sb = smem_base + stage * STAGE_BYTES;
-          const uint64_t a_hi = make_sw128_desc(sb);
-          const uint64_t a_lo = make_sw128_desc(sb + A_PLANE);
-          const uint64_t w_hi = make_sw128_desc(sb + 2 * A_PLANE);
-          const uint64_t w_lo = make_sw128_desc(sb + 2 * A_PLANE + W_PLANE);
+          const uint64_t a_hi = make_sw64_desc(sb);
+          const uint64_t a_lo = make_sw64_desc(sb + A_PLANE);
+          const uint64_t w_hi = make_sw64_desc(sb + 2 * A_PLANE);
+          const uint64_t w_lo = make_sw64_desc(sb + 2 * A_PLANE + W_PLANE);
 #pragma unroll
           for (int kk = 0; kk < BK / 16; ++kk) {
             const uint64_t adv = (uint64_t)(kk * 32 >> 4);    // 16 bf16 = 32 bytes along K
@@ -357,16 +372,16 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
       const bool r_vec = ((P.ldres & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.res) & 15) == 0);
       const bool m_vec = ((P.ldmul & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.mul) & 15) == 0);
       const bool o_vec = ((P.ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.O) & 15) == 0);
-      const int ncc = (P.Oh != nullptr) ? T.bn / 32 : min(T.bn / 32, (P.N - T.n0 + 31) / 32);   // planes carry the zero padding
-      const int nch_o = (P.N + 63) >> 6;       // 64-column chunks per row block of the output (and residual) planes
+      const int ncc = min(T.bn / 32, (P.N - T.n0 + 31) / 32);   // 32-column steps; a plane block is zero padded to 32
+      const int nch_o = (P.N + BK - 1) / BK;   // 32-column blocks per 128-row tile of the output (and residual) planes
       const bool res_planes = P.Rh != nullptr && row;
       float4 pr[8], pm[8];
       auto fetch = [&](int nb) {             // residual / multiplier columns nb..nb+31 of this thread's row
         if (res_planes) {                    // raw bf16 units: pr[0..3] hi, pr[4..7] lo (decoded where they are used)
-          const long long blk = ((long long)(T.m0 / BM) * nch_o + (nb >> 6)) * A_PLANE;
+          const long long blk = ((long long)(T.m0 / BM) * nch_o + (nb >> 5)) * A_PLANE;
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
-            const uint32_t off = sw128(rt, (((nb >> 5) & 1) << 2) + u);
+            const uint32_t off = sw64(rt, u);
             pr[u] = __ldg(reinterpret_cast<const float4*>(P.Rh + blk + off));
             pr[4 + u] = __ldg(reinterpret_cast<const float4*>(P.Rl + blk + off));
           }
@@ -471,8 +486,8 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
           }
         }
         if (P.Oh && row) {
-          // block (m-tile, 64-column chunk); this step covers 16-byte units (cc&1)*4 .. +3 of row rt
-          const long long blk = ((long long)(T.m0 / BM) * nch_o + (nb >> 6)) * A_PLANE;
+          // block (m-tile, 32-column chunk): this step is the whole 64-byte row rt of it
+          const long long blk = ((long long)(T.m0 / BM) * nch_o + (nb >> 5)) * A_PLANE;
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             uint4 h, l;
@@ -480,7 +495,7 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
             split2(v[8 * u + 2], v[8 * u + 3], h.y, l.y);
             split2(v[8 * u + 4], v[8 * u + 5], h.z, l.z);
             split2(v[8 * u + 6], v[8 * u + 7], h.w, l.w);
-            const uint32_t off = sw128(rt, ((cc & 1) << 2) + u);
+            const uint32_t off = sw64(rt, u);
             *reinterpret_cast<uint4*>(P.Oh + blk + off) = h;
             *reinterpret_cast<uint4*>(P.Ol + blk + off) = l;
           }
