@@ -60,10 +60,9 @@ struct Ws {
   float* hbuf;      // [R*12][128]
   float* xf;        // [R][kXS]   (only carved when with_io)
   float* yf;        // [R][kXS]
-  char* planeA;     // two buffers of bf16 hi/lo planes for Linear -> Linear activations (kernels.cuh LinProb::Ap)
+  char* planeA;     // buffers of bf16 hi|lo plane blocks for Linear -> Linear activations (kernels.cuh LinProb::Ap)
   char* planeB;
   char* planeR;     // the residual (bandFCs_pre output) when it lives only as planes (fused forward)
-  long long plane_lo;   // byte distance hi -> lo plane inside a buffer
   long long mtiles;     // 128-row tiles
 };
 // widest layer output in 32-column chunks summed over the 11 bands (bandFCs_back.2: 7 x 4 + 6 + 12 + 24 + 17 = 87)
@@ -90,12 +89,12 @@ size_t carve(Ws* w, char* base, long long R, bool with_io) {
   p = take((size_t)R * kBands * 2 * kGates); if (w) w->xproj = p;
   p = take((size_t)R * kBands * 2 * kFeat); if (w) w->hbuf = p;
   {
-    const long long mt = (R + 127) / 128;
+    const long long mt = ((R + 127) / 128 + 1) & ~1LL;   // even: a CTA pair always loads two 128-row tiles
     const size_t plane_floats = (size_t)mt * kPlaneChunksMax * kPlaneBlock / sizeof(float);
     p = take(2 * plane_floats); if (w) w->planeA = reinterpret_cast<char*>(p);
     p = take(2 * plane_floats); if (w) w->planeB = reinterpret_cast<char*>(p);
     p = take(2 * plane_floats); if (w) w->planeR = reinterpret_cast<char*>(p);
-    if (w) { w->plane_lo = (long long)plane_floats * sizeof(float); w->mtiles = mt; }
+    if (w) w->mtiles = mt;
   }
   if (with_io) {
     p = take((size_t)R * kXS); if (w) w->xf = p;
@@ -144,10 +143,10 @@ BandPlanes band_planes(const Ws& w, char* buf, WidthOf width_of) {
   BandPlanes b{};
   long long chunks = 0;
   for (int i = 0; i < kRealBands; ++i) {
-    b.band[i] = buf + w.mtiles * chunks * kPlaneBlock;
+    b.band[i] = buf + w.mtiles * chunks * (2 * kPlaneBlock);     // a block = hi then lo
     chunks += plane_chunks(width_of(i));
   }
-  b.lo = w.plane_lo;
+  b.lo = kPlaneBlock;
   return b;
 }
 inline void from_planes(LinProb& P, const BandPlanes& b, int i) { P.Ap = b.band[i]; P.a_lo = b.lo; P.A = nullptr; }
@@ -372,12 +371,12 @@ int run_rnn_block(int j, const float* fin, int C, int T, const void* packed, con
       a.h_step = ldh; a.h_seq = (long long)kBands * ldh;
       for (int d = 0; d < R.ndir; ++d) { a.wimg[d] = PW(packed, R.tcw[layer][d]); a.bias[d] = PW(packed, R.tcb[layer][d]); }
       a.nseq = C * T; a.nsteps = kBands; a.ndir = R.ndir;
-      if (layer == 1) { a.hplanes = w.planeA; a.hp_lo = w.plane_lo; }   // the fc below takes its A operand as planes
+      if (layer == 1) { a.hplanes = w.planeA; a.hp_lo = kPlaneBlock; }   // the fc below takes its A operand as planes
       CK(launch_lstm_tc(a, s));
       std::snprintf(nm, sizeof(nm), "rnn%d.rec%d", j, layer);
       mark(nm, s);
     }
-    CKI(single_linear(packed, R.fc, hl[1], ldh, fout, kFeat, rows, ACT_NONE, fin, kFeat, s, w.planeA, w.plane_lo));
+    CKI(single_linear(packed, R.fc, hl[1], ldh, fout, kFeat, rows, ACT_NONE, fin, kFeat, s, w.planeA, kPlaneBlock));
     std::snprintf(nm, sizeof(nm), "rnn%d.fc", j);
     mark(nm, s);
     return 0;
@@ -399,13 +398,13 @@ int run_rnn_block(int j, const float* fin, int C, int T, const void* packed, con
       if (st_in) { a.h0 = st_in + layer * per; a.c0 = st_in + (2 + layer) * per; }
       if (st_out) { a.hN = st_out + layer * per; a.cN = st_out + (2 + layer) * per; }
       const bool planes = layer == 1 && rows >= kTcMinRows;           // the fc below runs on the tensor-core kernel
-      if (planes) { a.hplanes = w.planeA; a.hp_lo = w.plane_lo; }
+      if (planes) { a.hplanes = w.planeA; a.hp_lo = kPlaneBlock; }
       CK(launch_lstm_seq(a, s));
       std::snprintf(nm, sizeof(nm), "rnn%d.rec%d", j, layer);
       mark(nm, s);
     }
     if (rows >= kTcMinRows)
-      CKI(single_linear(packed, R.fc, hl[1], ldh, fout, kFeat, rows, ACT_NONE, fin, kFeat, s, w.planeA, w.plane_lo));
+      CKI(single_linear(packed, R.fc, hl[1], ldh, fout, kFeat, rows, ACT_NONE, fin, kFeat, s, w.planeA, kPlaneBlock));
     else
       CKI(single_linear(packed, R.fc, hl[1], ldh, fout, kFeat, rows, ACT_NONE, fin, kFeat, s));
     std::snprintf(nm, sizeof(nm), "rnn%d.fc", j);

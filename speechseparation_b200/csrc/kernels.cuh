@@ -32,8 +32,9 @@ struct LinProb {
   int tiles_n;
   // Tensor-core path only: activations that go from one Linear straight into the next never exist as fp32
   // rows. The producing epilogue writes them as "planes": bf16 hi and lo (x = hi + lo), blocked as
-  // [m-tile of 128 rows][k-chunk of 32 columns][128 rows x 64 B, SWIZZLE_64B] = the shared-memory image the
-  // consuming layer's tcgen05.mma reads, so its A operand is two 8 KB bulk copies per chunk.
+  // [m-tile of 128 rows][k-chunk of 32 columns][hi | lo][128 rows x 64 B, SWIZZLE_64B] = the shared-memory image the
+  // consuming layer's tcgen05.mma reads, so its A operand is one 16 KB bulk copy per chunk. The *_lo offsets are the
+  // distance hi -> lo inside a block (kPlaneBlock).
   const void* Ap;      // optional input planes (hi at Ap, lo at Ap + a_lo); A may then be null
   void* Op;            // optional output planes (hi at Op, lo at Op + o_lo); O may then be null
   long long a_lo, o_lo;

@@ -212,7 +212,7 @@ lstm_seq_kernel(const __grid_constant__ LstmSeqArgs a) {
           // output row index, columns 4 part .. +3; the bf16 hi/lo pairs are already in the B-fragment buffers
           const long long m = (hoff + (long long)t * a.h_step) >> 6;
           const int r = (int)(m & 127);
-          uint8_t* p = reinterpret_cast<uint8_t*>(a.hplanes) + ((m >> 7) * 2 + (part >> 3)) * kPlaneBlock + sw64(r, (part & 7) >> 1) +
+          uint8_t* p = reinterpret_cast<uint8_t*>(a.hplanes) + ((m >> 7) * 2 + (part >> 3)) * (2 * kPlaneBlock) + sw64(r, (part & 7) >> 1) +
                        (part & 1) * 8;
           *reinterpret_cast<uint2*>(p) = *reinterpret_cast<const uint2*>(&hB[nxt][0][lseq][part * 4]);
           *reinterpret_cast<uint2*>(p + a.hp_lo) = *reinterpret_cast<const uint2*>(&hB[nxt][1][lseq][part * 4]);

@@ -183,7 +183,7 @@ lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
             // seq*nsteps + step; units 16 sl + 8 hf .. +7 of direction dir = chunk 2 dir + sl/2, 16-byte unit 2 (sl&1) + hf
             const long long m = seq * a.nsteps + step;
             const int r = (int)(m & 127);
-            uint8_t* p = reinterpret_cast<uint8_t*>(a.hplanes) + ((m >> 7) * (2 * a.ndir) + 2 * dir + (sl >> 1)) * kPlaneBlock +
+            uint8_t* p = reinterpret_cast<uint8_t*>(a.hplanes) + ((m >> 7) * (2 * a.ndir) + 2 * dir + (sl >> 1)) * (2 * kPlaneBlock) +
                          sw64(r, 2 * (sl & 1) + hf);
             *reinterpret_cast<uint4*>(p) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
             *reinterpret_cast<uint4*>(p + a.hp_lo) = make_uint4(lo[0], lo[1], lo[2], lo[3]);

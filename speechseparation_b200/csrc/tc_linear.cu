@@ -44,17 +44,24 @@ using namespace ptx;
 constexpr int BM = 128;              // rows per tile (UMMA M)
 constexpr int BK = kPlaneK;          // bf16 elements per K chunk = one 64-byte swizzle row (two k16 MMA steps)
 constexpr int BN_MAX = 256;          // columns per tile (UMMA N <= 256)
-constexpr int STAGES = 4;
 constexpr int A_PLANE = BM * BK * 2;         // bytes of one A plane per stage (8 KB) = kPlaneBlock
-constexpr int W_PLANE = BN_MAX * BK * 2;     // bytes of one W plane per stage (16 KB)
-constexpr int STAGE_BYTES = 2 * A_PLANE + 2 * W_PLANE;   // 48 KB
+// PAIR: two CTAs of a cluster (one TPC) run one tcgen05.mma.cta_group::2 tile of 256 rows: each CTA holds its own
+// 128 rows of A and HALF of the W rows, so a K chunk costs an SM 32 KB instead of 48 KB and six stages fit.
+template <bool PAIR> struct Smem {
+  static constexpr int W_PLANE = (PAIR ? BN_MAX / 2 : BN_MAX) * BK * 2;   // bytes of one W plane per stage (8 / 16 KB)
+  static constexpr int STAGE_BYTES = 2 * A_PLANE + 2 * W_PLANE;           // 32 / 48 KB
+  static constexpr int STAGES = PAIR ? 6 : 4;
+};
+constexpr int MAX_STAGES = 6;
 // Warp roles (setmaxnreg works per warpgroup = 4 consecutive warps):
 //   fp32-row A (A_PLANES = false), 24 warps at 80 registers:
 //     warps 0-7   A producer group 0 (fills stage 0)      warps 8-15  A producer group 1 (fills stage 1)
-//     warp 16     MMA issuer (+ TMEM alloc)               warp 17     loader            warps 18, 19 idle
+//     warp 16     MMA issuer (+ TMEM alloc)               warps 17, 18  W loaders (hi, lo)   warp 19 idle
 //     warps 20-23 epilogue, grown to 152 registers
 //   plane A (A_PLANES = true), 12 warps, no register re-partitioning needed:
-//     warp 0 MMA issuer, warp 1 loader (A and W by bulk copy), warps 2, 3 idle, warps 4-11 epilogue
+//     warp 0 MMA issuer, warps 1-3 loaders (A hi|lo, W hi, W lo: one bulk copy each per stage), warps 4-11 epilogue
+// A thread's cp.async.bulk requests are served one at a time, ~540 cycles each whatever their size up to 32 KB
+// (tools/mem_bench.cu), requests of different warps concurrently: one loader warp per piece of a stage.
 // An epilogue warp may read the TMEM lane quarter warp % 4; with 8 epilogue warps the two warps of a quarter
 // take alternate 32-column chunks.
 // Two producer groups, each with its own register-resident chunk in flight: the global-load latency of one
@@ -68,10 +75,9 @@ template <bool A_PLANES> struct Roles {
   static constexpr int N_EPI_WARPS = A_PLANES ? 8 : 4;
   static constexpr int THREADS = (EPI_WARP0 + N_EPI_WARPS) * 32;
 };
-template <bool A_PLANES> constexpr int smem_bytes() { return STAGES * STAGE_BYTES + 1024; }   // + alignment slack
-constexpr int N_PRODUCERS = N_GROUP_WARPS * 32;               // 256 threads fill one stage
+template <bool PAIR> constexpr int smem_bytes() { return Smem<PAIR>::STAGES * Smem<PAIR>::STAGE_BYTES + 1024; }   // + alignment slack
 constexpr int REGS_PRODUCER = 64, REGS_CONTROL = 40, REGS_EPILOGUE = 184;   // released 512*16 + 128*40 = taken 128*104
-static_assert(STAGES == 4 && A_PLANE == kPlaneBlock, "two producer groups alternate over four stages");
+static_assert(Smem<false>::STAGES == 4 && A_PLANE == kPlaneBlock, "two producer groups alternate over four stages");
 constexpr int TMEM_COLS = 512;       // 2 accumulators x 256 fp32 columns
 
 struct TcProb {
@@ -103,15 +109,17 @@ struct Tile {
   int pi, m0, n0, bn;    // problem, first row, first column, columns in this tile (multiple of 64)
 };
 
-__device__ __forceinline__ Tile decode_tile(const TcArgs& args, int tile) {
-  int pi = 0;
+// tile_rows = 128, rank 0 for single CTAs; 256 and the CTA's rank in the pair for cta_group::2
+// `pi` carries the problem index from one tile of a role to its next (tiles of a CTA ascend), so the walk over
+// the problem table is amortised: from scratch it costs ~10 dependent constant-bank loads for the widest bands.
+__device__ __forceinline__ Tile decode_tile(const TcArgs& args, int tile, int& pi, int tile_rows = BM, int rank = 0) {
   while (pi + 1 < args.nprob && tile >= args.p[pi + 1].tile_start) ++pi;
   const TcProb& P = args.p[pi];
   const int local = tile - P.tile_start;
   Tile t;
   t.pi = pi;
   const int tiles_n = (P.N + BN_MAX - 1) / BN_MAX;
-  t.m0 = (local / tiles_n) * BM;              // n fastest: the CTAs of a wave read different W blocks
+  t.m0 = (local / tiles_n) * tile_rows + rank * BM;   // n fastest: the CTAs of a wave read different W blocks
   t.n0 = (local % tiles_n) * BN_MAX;
   const int npad = (P.N + 63) & ~63;
   t.bn = min(BN_MAX, npad - t.n0);
@@ -183,9 +191,9 @@ __device__ unsigned long long* g_trace = nullptr;
 #define TRACE_DECL int trace_n = 0
 #define TRACE(role, code)                                                            \
   do {                                                                               \
-    if (blockIdx.x == 0 && args.trace && g_trace != nullptr && trace_n < 3000) {                   \
-      g_trace[(role) * 6000 + 2 * trace_n] = (unsigned long long)(code);             \
-      g_trace[(role) * 6000 + 2 * trace_n + 1] = (unsigned long long)clock64();      \
+    if (blockIdx.x <= 1 && args.trace && g_trace != nullptr && trace_n < 3000) {                   \
+      g_trace[((role) + 5 * blockIdx.x) * 6000 + 2 * trace_n] = (unsigned long long)(code);             \
+      g_trace[((role) + 5 * blockIdx.x) * 6000 + 2 * trace_n + 1] = (unsigned long long)clock64();      \
       ++trace_n;                                                                     \
     }                                                                                \
   } while (0)
@@ -197,14 +205,25 @@ __device__ unsigned long long* g_trace = nullptr;
 
 // A_PLANES: every problem of the launch takes its A operand from bf16 planes (two bulk copies per chunk by the
 // loader thread); the 16 producer warps then have no work and only the loader arrives on the full barrier.
-template <bool A_PLANES>
+// PAIR (with A_PLANES only): launched as clusters of two CTAs; CTA rank 0 issues the MMAs for both, every CTA loads
+// its own operands, drains its own 128 accumulator rows and reports to rank 0:
+//   bar_full[s]   own bulk copies of stage s landed        bar_peer[s] (rank 0)  rank 1's stage s landed (relayed by its warp 0)
+//   bar_empty[s]  MMAs reading stage s retired (commit multicast to both CTAs)
+//   bar_tfull[a]  accumulator a complete (commit multicast) bar_tempty[a] (rank 0) drained by all 16 epilogue warps
+template <bool A_PLANES, bool PAIR>
 __global__ void __launch_bounds__(Roles<A_PLANES>::THREADS, 1)
 tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
+  static_assert(A_PLANES || !PAIR, "the CTA-pair kernel takes its A operand from planes");
   using R = Roles<A_PLANES>;
   constexpr int MMA_WARP = R::MMA_WARP, W_WARP = R::LOAD_WARP, EPI_WARP0 = R::EPI_WARP0, N_EPI_WARPS = R::N_EPI_WARPS;
+  constexpr int STAGES = Smem<PAIR>::STAGES, STAGE_BYTES = Smem<PAIR>::STAGE_BYTES, W_PLANE = Smem<PAIR>::W_PLANE;
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bar_full[STAGES], bar_empty[STAGES], bar_tfull[2], bar_tempty[2];
+  __shared__ __align__(8) uint64_t bar_full[MAX_STAGES], bar_empty[MAX_STAGES], bar_peer[MAX_STAGES], bar_tfull[2], bar_tempty[2];
   __shared__ uint32_t tmem_slot;
+  const int rank = PAIR ? (int)cluster_ctarank() : 0;
+  const int tile0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;          // first tile and stride of this CTA / pair
+  const int tile_step = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  constexpr int TILE_ROWS = PAIR ? 2 * BM : BM;
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
@@ -214,21 +233,27 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
 
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) {
-      mbar_init(smem_u32(&bar_full[s]), A_PLANES ? 1 : N_PRODUCERS + 1);   // the loader's expect_tx arrive (+ producers)
+      mbar_init(smem_u32(&bar_full[s]), A_PLANES ? 3 : N_GROUP_WARPS + 2);   // the loaders' expect_tx arrives (+ one arrive per producer warp)
       mbar_init(smem_u32(&bar_empty[s]), 1);
+      mbar_init(smem_u32(&bar_peer[s]), 1);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(smem_u32(&bar_tfull[a]), 1);
-      mbar_init(smem_u32(&bar_tempty[a]), N_EPI_WARPS * 32);
+      mbar_init(smem_u32(&bar_tempty[a]), PAIR ? 2 * N_EPI_WARPS : N_EPI_WARPS * 32);   // pair: one lane per epilogue warp of both CTAs
     }
     fence_mbar_init();
   }
   if (warp == MMA_WARP) {
-    tmem_alloc(smem_u32(&tmem_slot), TMEM_COLS);
-    tmem_relinquish();
+    if (PAIR) {
+      tmem_alloc_pair(smem_u32(&tmem_slot), TMEM_COLS);
+      tmem_relinquish_pair();
+    } else {
+      tmem_alloc(smem_u32(&tmem_slot), TMEM_COLS);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
   TRACE_DECL;
@@ -239,11 +264,11 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
     setmaxnreg_dec<REGS_PRODUCER>();
     const int grp = warp / N_GROUP_WARPS;
     const int pt = (warp % N_GROUP_WARPS) * 32 + lane;      // thread 0..255 of the group
-    int tile = blockIdx.x, kc = 0, nk = 0;
+    int tile = blockIdx.x, kc = 0, nk = 0, pi = 0;
     Tile T{};
     auto open_tile = [&]() {
       if (tile < args.total_tiles) {
-        T = decode_tile(args, tile);
+        T = decode_tile(args, tile, pi);
         nk = (args.p[T.pi].K + BK - 1) / BK;
       }
     };
@@ -267,61 +292,93 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
         if (h == 1 && !second) break;
         const int stage = 2 * grp + h;
         uint8_t* sb = smem_gen + stage * STAGE_BYTES;
-        mbar_wait(smem_u32(&bar_empty[stage]), phase ^ 1);
+        // one lane per warp talks to the barriers: 32x fewer polls and arrives on the CTA's barrier unit
+        if (lane == 0) mbar_wait(smem_u32(&bar_empty[stage]), phase ^ 1);
+        __syncwarp();
         if (pt == 0) TRACE(grp ? 3 : 0, 1 + 100 * grp);
         store_a(h == 0 ? r0 : r1, sb, sb + A_PLANE, pt);
         fence_proxy_async_smem();
-        mbar_arrive(smem_u32(&bar_full[stage]));
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&bar_full[stage]));
         if (pt == 0) TRACE(grp ? 3 : 0, 3 + 100 * grp);
       }
       phase ^= 1;
     }
   } else if (warp < EPI_WARP0) {
     if (!A_PLANES) setmaxnreg_dec<REGS_CONTROL>();
-    if (warp == W_WARP && lane == 0) {
-      // ================= W loader (one thread) =================
+    constexpr int N_LOADERS = A_PLANES ? 3 : 2;
+    if (warp >= W_WARP && warp < W_WARP + N_LOADERS) {
+      // ================= loaders: one warp (one thread) per piece of a stage =================
+      //   A_PLANES: piece 0 = A block (hi|lo, 16 KB), 1 = W hi, 2 = W lo;   fp32 A: piece 1 = W hi, 2 = W lo
+      const int piece = warp - W_WARP + (A_PLANES ? 0 : 1);
+      if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
-        const Tile T = decode_tile(args, tile);
+      int pi = 0;
+      for (int tile = tile0; tile < args.total_tiles; tile += tile_step) {
+        const Tile T = decode_tile(args, tile, pi, TILE_ROWS, rank);
         const TcProb& P = args.p[T.pi];
         const int nk = (P.K + BK - 1) / BK;
         for (int kc = 0; kc < nk; ++kc) {
           mbar_wait(smem_u32(&bar_empty[stage]), phase ^ 1);
-          TRACE(4, 30 + stage);
-          // W blocks [bn x 64] bf16, already swizzled: (n0 * nch + kc * bn) * 128 bytes into each plane
-          const uint32_t bytes = (uint32_t)T.bn * (BK * 2);
-          const long long off = ((long long)T.n0 * (P.ldw >> 5) + (long long)kc * T.bn) * (BK * 2);
+          if (piece == 0) TRACE(4, 30 + stage);
           const uint32_t bar = smem_u32(&bar_full[stage]);
-          mbar_arrive_expect_tx(bar, 2 * bytes + (A_PLANES ? 2 * A_PLANE : 0));
-          if (A_PLANES) {
-            const long long aoff = ((long long)(T.m0 / BM) * nk + kc) * A_PLANE;
-            bulk_g2s(smem_base + stage * STAGE_BYTES, P.Ah + aoff, A_PLANE, bar);
-            bulk_g2s(smem_base + stage * STAGE_BYTES + A_PLANE, P.Al + aoff, A_PLANE, bar);
+          const uint32_t sb = smem_base + stage * STAGE_BYTES;
+          if (piece == 0) {
+            // plane block (m-tile, chunk): hi then lo, 16 KB
+            const long long aoff = ((long long)(T.m0 / BM) * nk + kc) * (2 * A_PLANE);
+            mbar_arrive_expect_tx(bar, 2 * A_PLANE);
+            bulk_g2s(sb, P.Ah + aoff, 2 * A_PLANE, bar);
+          } else {
+            // W blocks [bn x 32] bf16, already swizzled: (n0 * nch + kc * bn) * 64 bytes into the plane; a CTA of a
+            // pair takes the rows of its half of the tile's columns
+            const uint32_t wrows = PAIR ? (uint32_t)T.bn >> 1 : (uint32_t)T.bn;
+            const uint32_t bytes = wrows * (BK * 2);
+            const long long off = ((long long)T.n0 * (P.ldw >> 5) + (long long)kc * T.bn + (long long)rank * wrows) * (BK * 2);
+            const uint8_t* src = reinterpret_cast<const uint8_t*>(piece == 1 ? P.Wh : P.Wl) + off;
+            mbar_arrive_expect_tx(bar, bytes);
+            bulk_g2s(sb + 2 * A_PLANE + (piece == 2 ? W_PLANE : 0), src, bytes, bar);
           }
-          bulk_g2s(smem_base + stage * STAGE_BYTES + 2 * A_PLANE, reinterpret_cast<const uint8_t*>(P.Wh) + off, bytes, bar);
-          bulk_g2s(smem_base + stage * STAGE_BYTES + 2 * A_PLANE + W_PLANE, reinterpret_cast<const uint8_t*>(P.Wl) + off, bytes, bar);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
-    } else if (warp == MMA_WARP) {
+      }
+    } else if (PAIR && warp == MMA_WARP && rank == 1) {
+      // ================= relay (rank 1): "my stage s has landed" -> rank 0 =================
+      int stage = 0;
+      uint32_t phase = 0;
+      int pi = 0;
+      for (int tile = tile0; tile < args.total_tiles; tile += tile_step) {
+        const Tile T = decode_tile(args, tile, pi, TILE_ROWS, rank);
+        const int nk = (args.p[T.pi].K + BK - 1) / BK;
+        for (int kc = 0; kc < nk; ++kc) {
+          if (lane == 0) {
+            mbar_wait(smem_u32(&bar_full[stage]), phase);
+            mbar_arrive_cluster(map_to_cta(smem_u32(&bar_peer[stage]), 0));
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    } else if (warp == MMA_WARP && rank == 0) {
     // ================= MMA issuer =================
+    // The warp stays converged (every value below is warp-uniform) and one elected lane issues: see elect_one().
+    {
     int stage = 0, acc = 0;
     uint32_t phase = 0, acc_phase = 0;
-    for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
-      const Tile T = decode_tile(args, tile);
+    int pi = 0;
+    for (int tile = tile0; tile < args.total_tiles; tile += tile_step) {
+      const Tile T = decode_tile(args, tile, pi, TILE_ROWS, rank);
       const TcProb& P = args.p[T.pi];
       const int nk = (P.K + BK - 1) / BK;
       mbar_wait(smem_u32(&bar_tempty[acc]), acc_phase ^ 1);   // epilogue has drained this accumulator
-      if (lane == 0) TRACE(1, 10);
       tc_fence_after();
-      const uint32_t idesc = make_idesc_bf16(BM, T.bn);
+      const uint32_t idesc = make_idesc_bf16(TILE_ROWS, T.bn);
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN_MAX);
       for (int kc = 0; kc < nk; ++kc) {
         mbar_wait(smem_u32(&bar_full[stage]), phase);
-        if (lane == 0) TRACE(1, 11);
+        if (PAIR) mbar_wait(smem_u32(&bar_peer[stage]), phase);   // the peer's half of the stage (no data read by this thread)
         tc_fence_after();
-        if (lane == 0) {
+        if (elect_one()) {
           const uint32_t sb = smem_base + stage * STAGE_BYTES;
           const uint64_t a_hi = make_sw64_desc(sb);
           const uint64_t a_lo = make_sw64_desc(sb + A_PLANE);
@@ -330,18 +387,29 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
 #pragma unroll
           for (int kk = 0; kk < BK / 16; ++kk) {
             const uint64_t adv = (uint64_t)(kk * 32 >> 4);    // 16 bf16 = 32 bytes along K
-            mma_bf16_ss(d_tmem, a_lo + adv, w_hi + adv, idesc, (kc | kk) != 0);   // small terms first
-            mma_bf16_ss(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
-            mma_bf16_ss(d_tmem, a_hi + adv, w_hi + adv, idesc, 1);
+            if (PAIR) {
+              mma_bf16_ss_pair(d_tmem, a_lo + adv, w_hi + adv, idesc, (kc | kk) != 0);
+              mma_bf16_ss_pair(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
+              mma_bf16_ss_pair(d_tmem, a_hi + adv, w_hi + adv, idesc, 1);
+            } else {
+              mma_bf16_ss(d_tmem, a_lo + adv, w_hi + adv, idesc, (kc | kk) != 0);   // small terms first
+              mma_bf16_ss(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
+              mma_bf16_ss(d_tmem, a_hi + adv, w_hi + adv, idesc, 1);
+            }
           }
-          mma_commit(smem_u32(&bar_empty[stage]));             // smem stage reusable once these MMAs retire
-          if (kc == nk - 1) mma_commit(smem_u32(&bar_tfull[acc]));
-          TRACE(1, 12);
+          if (PAIR) {
+            mma_commit_pair(smem_u32(&bar_empty[stage]), 3);   // both CTAs' stage s reusable once these MMAs retire
+            if (kc == nk - 1) mma_commit_pair(smem_u32(&bar_tfull[acc]), 3);
+          } else {
+            mma_commit(smem_u32(&bar_empty[stage]));           // smem stage reusable once these MMAs retire
+            if (kc == nk - 1) mma_commit(smem_u32(&bar_tfull[acc]));
+          }
         }
         __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
     }
     }
   } else {
@@ -360,8 +428,9 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
     const int rt = q * 32 + lane;           // row of the tile
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
-      const Tile T = decode_tile(args, tile);
+    int pi = 0;
+    for (int tile = tile0; tile < args.total_tiles; tile += tile_step) {
+      const Tile T = decode_tile(args, tile, pi, TILE_ROWS, rank);
       const TcProb& P = args.p[T.pi];
       const int m = T.m0 + rt;
       const bool row = m < P.M;
@@ -378,7 +447,7 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
       float4 pr[8], pm[8];
       auto fetch = [&](int nb) {             // residual / multiplier columns nb..nb+31 of this thread's row
         if (res_planes) {                    // raw bf16 units: pr[0..3] hi, pr[4..7] lo (decoded where they are used)
-          const long long blk = ((long long)(T.m0 / BM) * nch_o + (nb >> 5)) * A_PLANE;
+          const long long blk = ((long long)(T.m0 / BM) * nch_o + (nb >> 5)) * (2 * A_PLANE);
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             const uint32_t off = sw64(rt, u);
@@ -416,7 +485,8 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
       const bool has_rm = rrow != nullptr || mrow != nullptr || res_planes;
       int cc = ew >> 2;
       if (has_rm && cc < ncc) fetch(T.n0 + cc * 32);
-      mbar_wait(smem_u32(&bar_tfull[acc]), acc_phase);
+      if (lane == 0) mbar_wait(smem_u32(&bar_tfull[acc]), acc_phase);
+      __syncwarp();
       if (ew == BSB_TRACE_EPI && lane == 0) TRACE(2, 20);
       tc_fence_after();
       const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN_MAX);
@@ -486,8 +556,8 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
           }
         }
         if (P.Oh && row) {
-          // block (m-tile, 32-column chunk): this step is the whole 64-byte row rt of it
-          const long long blk = ((long long)(T.m0 / BM) * nch_o + (nb >> 5)) * A_PLANE;
+          // block (m-tile, 32-column chunk), hi then lo: this step is the whole 64-byte row rt of both
+          const long long blk = ((long long)(T.m0 / BM) * nch_o + (nb >> 5)) * (2 * A_PLANE);
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             uint4 h, l;
@@ -503,21 +573,30 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
         if (ew == BSB_TRACE_EPI && lane == 0) TRACE(2, 24);
       }
       tc_fence_before();
-      mbar_arrive(smem_u32(&bar_tempty[acc]));
+      if (PAIR) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(map_to_cta(smem_u32(&bar_tempty[acc]), 0));
+      } else {
+        mbar_arrive(smem_u32(&bar_tempty[acc]));
+      }
       if (ew == BSB_TRACE_EPI && lane == 0) TRACE(2, 21);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all(); else __syncthreads();   // the peer may still arrive on this CTA's barriers / read its smem
   if (warp == MMA_WARP) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    if (PAIR) tmem_dealloc_pair(tmem_base, TMEM_COLS); else tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 
 int g_sm_count[64] = {};
+// Plane-operand launches on CTA pairs (cta_group::2, 256-row tiles, each CTA loads half of the W rows) are verified
+// bit-identical to the single-CTA path but measured slower on this workload (5.2 vs 4.5 ms/step, profiles/
+// r01_summary.md): opt-in for experiments.
+const bool g_pair = getenv("BSB_PAIR") != nullptr;
 
 }  // namespace
 
@@ -526,9 +605,11 @@ int g_sm_count[64] = {};
 cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(tc_grouped_linear_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<false>());
+    cudaError_t e = cudaFuncSetAttribute(tc_grouped_linear_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<false>());
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(tc_grouped_linear_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<true>());
+    e = cudaFuncSetAttribute(tc_grouped_linear_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<false>());
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(tc_grouped_linear_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<true>());
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
@@ -550,6 +631,10 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
     }
   TcArgs ta{};
   int total = 0, n_planes = 0;
+  for (int i = 0; i < n; ++i) n_planes += args.p[order[i]].Ap != nullptr;
+  if (n_planes != 0 && n_planes != n) return cudaErrorInvalidValue;   // one A source per launch
+  const bool pair = n_planes != 0 && g_pair;                      // plane operands: CTA pairs, 256-row tiles
+  const int tile_rows = pair ? 2 * BM : BM;
   for (int i = 0; i < n; ++i) {
     const LinProb& L = args.p[order[i]];
     TcProb& P = ta.p[i];
@@ -559,13 +644,12 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
     P.Ol = L.Op ? P.Oh + L.o_lo : nullptr;
     P.Rh = reinterpret_cast<const uint8_t*>(L.Rp);
     P.Rl = L.Rp ? P.Rh + L.r_lo : nullptr;
-    n_planes += L.Ap != nullptr;
     P.A = L.A; P.Wh = reinterpret_cast<const __nv_bfloat16*>(L.Wh); P.Wl = reinterpret_cast<const __nv_bfloat16*>(L.Wl);
     P.bias = L.bias; P.O = L.O; P.res = L.res; P.mul = L.mul;
     P.lda = L.lda; P.ldw = L.ldw64; P.ldo = L.ldo; P.ldres = L.ldres; P.ldmul = L.ldmul;
     P.M = L.M; P.N = L.N; P.K = L.K; P.act = L.act;
     P.tile_start = total;
-    P.tiles_m = (L.M + BM - 1) / BM;
+    P.tiles_m = (L.M + tile_rows - 1) / tile_rows;
     total += P.tiles_m * ((L.N + BN_MAX - 1) / BN_MAX);
   }
   ta.nprob = n;
@@ -577,12 +661,27 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
 #endif
 
   if (total == 0) return cudaSuccess;
-  if (n_planes != 0 && n_planes != n) return cudaErrorInvalidValue;   // one A source per launch
+  if (pair) {
+    const int pairs = total < sms / 2 ? total : sms / 2;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(2 * pairs);
+    cfg.blockDim = dim3(Roles<true>::THREADS);
+    cfg.dynamicSmemBytes = smem_bytes<true>();
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    e = cudaLaunchKernelEx(&cfg, tc_grouped_linear_kernel<true, true>, ta);
+    count_launch();
+    return e != cudaSuccess ? e : cudaGetLastError();
+  }
   const int grid = total < sms ? total : sms;
   if (n_planes)
-    tc_grouped_linear_kernel<true><<<grid, Roles<true>::THREADS, smem_bytes<true>(), s>>>(ta);
+    tc_grouped_linear_kernel<true, false><<<grid, Roles<true>::THREADS, smem_bytes<false>(), s>>>(ta);
   else
-    tc_grouped_linear_kernel<false><<<grid, Roles<false>::THREADS, smem_bytes<false>(), s>>>(ta);
+    tc_grouped_linear_kernel<false, false><<<grid, Roles<false>::THREADS, smem_bytes<false>(), s>>>(ta);
   count_launch();
   return cudaGetLastError();
 }

@@ -55,6 +55,39 @@ __global__ void __launch_bounds__(128, 1) bulk_stream(const uint8_t* g, long lon
   }
 }
 
+// `nissue` threads (lane 0 of warps 0..nissue-1, or lanes 0..nissue-1 of warp 0 when same_warp) each keep their own
+// ring of `stages` bulk copies of `bytes` in flight: are requests of different threads served concurrently?
+__global__ void __launch_bounds__(256, 1) bulk_multi(const uint8_t* g, long long nbytes, int nissue, int same_warp, int stages, int bytes, int iters,
+                                                     long long* out) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bar[8][8];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  if (threadIdx.x == 0) { for (int i = 0; i < 64; ++i) mbar_init(smem_u32(&bar[i / 8][i % 8]), 1); fence_mbar_init(); }
+  __syncthreads();
+  const int me = same_warp ? (int)threadIdx.x : (int)(threadIdx.x >> 5);
+  const bool issuer = same_warp ? (threadIdx.x < nissue) : ((threadIdx.x & 31) == 0 && me < nissue);
+  if (issuer) {
+    long long off = ((long long)blockIdx.x * nissue + me) * bytes;
+    const long long stride = (long long)gridDim.x * nissue * bytes;
+    const uint32_t mybase = base + me * stages * bytes;
+    auto issue = [&](int s) {
+      mbar_arrive_expect_tx(smem_u32(&bar[me][s]), bytes);
+      bulk_g2s(mybase + s * bytes, g + (off % nbytes), bytes, smem_u32(&bar[me][s]));
+      off += stride;
+    };
+    const long long t0 = clock64();
+    for (int s = 0; s < stages; ++s) issue(s);
+    int s = 0; uint32_t ph = 0;
+    for (int it = 0; it < iters; ++it) {
+      mbar_wait(smem_u32(&bar[me][s]), ph);
+      if (it + stages < iters) issue(s);
+      if (++s == stages) { s = 0; ph ^= 1; }
+    }
+    const long long t1 = clock64();
+    if (blockIdx.x == 0 && me == 0) out[0] = t1 - t0;
+  }
+}
+
 int main() {
   long long* d; cudaMalloc(&d, 16);
   float* sink; cudaMalloc(&sink, 4);
@@ -78,6 +111,23 @@ int main() {
       printf("bulk     %d x %2d KB (%2d pieces of %5d B) = %3d KB in flight : %6.1f B/clk/SM (%s)\n", stages, bytes >> 10, pieces, bytes / pieces,
              stages * bytes >> 10, 600.0 * bytes / h, cudaGetErrorString(cudaGetLastError()));
     }
+  }
+  printf("---- request size (L2 resident source), pieces = 1\n");
+  for (int bytes : {4096, 8192, 16384, 32768, 65536}) for (int stages : {2, 3, 6, 8}) {
+    if (stages * bytes > 196608 || stages > 8) continue;
+    for (int rep = 0; rep < 2; ++rep) { bulk_stream<<<148, 128, 200 * 1024>>>(g, small, stages, bytes, 1, 600, d); cudaDeviceSynchronize(); }
+    cudaMemcpy(&h, d, 8, cudaMemcpyDeviceToHost);
+    printf("bulk %d x %2d KB in flight : %6.1f B/clk/SM, %6.0f cycles per request (%s)\n", stages, bytes >> 10, 600.0 * bytes / h, (double)h / 600,
+           cudaGetErrorString(cudaGetLastError()));
+  }
+  printf("---- issuing threads (L2 resident source), 2 requests in flight per thread\n");
+  cudaFuncSetAttribute(bulk_multi, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  for (int same_warp : {0, 1}) for (int bytes : {8192, 16384}) for (int nissue : {1, 2, 4}) {
+    if (nissue * 2 * bytes > 196608) continue;
+    for (int rep = 0; rep < 2; ++rep) { bulk_multi<<<148, 256, 200 * 1024>>>(g, small, nissue, same_warp, 2, bytes, 600, d); cudaDeviceSynchronize(); }
+    cudaMemcpy(&h, d, 8, cudaMemcpyDeviceToHost);
+    printf("%d issuing %s x 2 x %2d KB : %6.1f B/clk/SM, %6.0f cycles per request per thread (%s)\n", nissue, same_warp ? "lanes of one warp" : "warps (lane 0)",
+           bytes >> 10, 600.0 * bytes * nissue / h, (double)h / 600, cudaGetErrorString(cudaGetLastError()));
   }
   printf("---- every SM streams the same addresses (weights): 4 MB region, 2 x 32 KB in flight\n");
   for (int groups : {1, 2, 4, 16, 148}) {

@@ -19,21 +19,21 @@ s = torch.cuda.current_stream().cuda_stream
 for _ in range(2):
     _lib.check(l.bsb_bandsplit(xf.data_ptr(), R, packed.data_ptr(), residual.data_ptr(), feat.data_ptr(), ws.data_ptr(), ws.numel(), s))
 torch.cuda.synchronize()
-tr = torch.zeros(5 * 6000, dtype=torch.int64, device="cuda")
+tr = torch.zeros(10 * 6000, dtype=torch.int64, device="cuda")
 l.bsb_debug_set_trace(tr.data_ptr())
 _lib.check(l.bsb_bandsplit(xf.data_ptr(), R, packed.data_ptr(), residual.data_ptr(), feat.data_ptr(), ws.data_ptr(), ws.numel(), s))
 torch.cuda.synchronize()
 l.bsb_debug_set_trace(None)
 t = tr.cpu().tolist()
 ev = []
-for role in range(5):
+for role in range(10):
     for i in range(3000):
         code, clk = t[role * 6000 + 2 * i], t[role * 6000 + 2 * i + 1]
-        if code: ev.append((clk, code))
+        if code: ev.append((clk, code + (1000 if role >= 5 else 0)))
 ev.sort()
 n = len(ev)
 t0 = ev[0][0]
-names = {1: "P0 empty-acq", 3: "P0 arrived", 4: "P0 loads-issued", 101: "P1 empty-acq", 103: "P1 arrived", 104: "P1 loads-issued", 30: "W issue s0", 31: "W issue s1", 10: "M tempty-acq", 11: "M full-acq", 12: "M issued", 20: "E tfull-acq", 21: "E done", 22: "E loads-issued", 23: "E tmem-read", 24: "E chunk-done"}
+names = {1: "P0 empty-acq", 3: "P0 arrived", 4: "P0 loads-issued", 101: "P1 empty-acq", 103: "P1 arrived", 104: "P1 loads-issued", 30: "W issue s0", 31: "W issue s1", 10: "M tempty-acq", 13: "M full-own", 1014: "R1 relay full", 11: "M full-acq", 12: "M issued", 20: "E tfull-acq", 21: "E done", 22: "E loads-issued", 23: "E tmem-read", 24: "E chunk-done"}
 with open("gpurun_out/trace_tc.txt", "w") as f:
     for c, code in ev[:9000]:
         f.write(f"{c - t0:9d} {names.get(code, code)}\n")
