@@ -15,6 +15,7 @@
 #include <mutex>
 #include <vector>
 #include "kernels.cuh"
+#include "ptx.cuh"
 
 namespace bsb {
 namespace {
@@ -100,6 +101,7 @@ __device__ __forceinline__ void irfft_split_load(const float* in, const float2* 
 //   X[k1 + 32 k2] = sum_l W32^(l k2) * ( W1024^(l k1) * sum_j z[l + 32 j] W32^(j k1) )
 constexpr int kFrameWarps = 4;                 // frames (warps) per CTA
 constexpr int kTr = 33;                        // transpose row stride (float2)
+constexpr int kTw32 = 2 * 1024 + 1;            // offset of the [32][32] inter-stage twiddle table in the twiddle array
 
 __device__ __forceinline__ constexpr int br5(int i) {
   return ((i & 1) << 4) | ((i & 2) << 2) | (i & 4) | ((i & 8) >> 2) | ((i & 16) >> 4);
@@ -153,7 +155,7 @@ __device__ __forceinline__ void warp_fft1024(float2 (&v)[32], float2* tr, const 
   for (int k1 = 0; k1 < 32; ++k1) {
     float2 y = v[br5(k1)];
     if (k1 > 0) {
-      float2 w = __ldg(tw + lane * k1);
+      float2 w = __ldg(tw + kTw32 + k1 * 32 + lane);   // W_1024^(lane k1), stored k1-major: one 256-byte run per load
       if (INV) w.y = -w.y;
       y = cmul(y, w);
     }
@@ -223,11 +225,23 @@ stft_warp_kernel(const float* __restrict__ wav, long long L, int T, int nrows, c
 
 // A warp produces `per` consecutive 1024-sample output blocks of one row; the windowed second
 // half of the previous frame stays in registers (same lane, same slot as the next first half).
-__global__ void __launch_bounds__(kFrameWarps * 32, 4)
+// STAGED: the frame's spectrum row (8,200 B, padded to 8,208) is brought into shared memory by one bulk copy
+// (cp.async.bulk, completion on a per-warp mbarrier) that is issued for frame f+1 as soon as frame f has been
+// read into registers, so the HBM latency of a frame hides under the ~3k instructions of the previous one;
+// the direct variant (any row stride / alignment) issues its loads at the top of the frame and waits for them.
+constexpr int kStageFloats = 2052;             // 2050 rounded up to a multiple of 16 bytes
+constexpr int kIstftWarpSmem = 32 * kTr * 8 + kStageFloats * 4;   // transpose tile + staged row, per warp
+
+template <bool STAGED>
+__global__ void __launch_bounds__(kFrameWarps * 32, STAGED ? 3 : 4)
 istft_warp_kernel(const float* __restrict__ xf, int xs, int T, int nseg, int nwork, const float* __restrict__ win,
                   const float2* __restrict__ tw, float* __restrict__ wav, int per) {
-  __shared__ __align__(16) float2 tr_all[kFrameWarps][32 * kTr];
+  extern __shared__ __align__(16) uint8_t istft_smem[];
+  __shared__ __align__(8) uint64_t bar_all[kFrameWarps];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float2* tr = reinterpret_cast<float2*>(istft_smem + (size_t)warp * (STAGED ? kIstftWarpSmem : 32 * kTr * 8));
+  const float* stage = reinterpret_cast<const float*>(tr + 32 * kTr);
+  const uint32_t bar = ptx::smem_u32(&bar_all[warp]);
   const int wk = blockIdx.x * kFrameWarps + warp;          // (row, segment)
   if (wk >= nwork) return;
   const int c = wk / nseg, b0 = (wk - c * nseg) * per;
@@ -237,16 +251,32 @@ istft_warp_kernel(const float* __restrict__ xf, int xs, int T, int nseg, int nwo
   const float inv_m = 1.0f / kM;
   const float2* tw2 = tw + kM;
   const float2* win2 = reinterpret_cast<const float2*>(win);
+  if (STAGED) {
+    if (lane == 0) {
+      ptx::mbar_init(bar, 1);
+      ptx::fence_mbar_init();
+      ptx::mbar_arrive_expect_tx(bar, kStageFloats * 4);
+      ptx::bulk_g2s(ptx::smem_u32(stage), xf + ((long long)c * T + b0) * xs, kStageFloats * 4, bar);
+    }
+    __syncwarp();
+  }
   float2 prev[16];
   float2 v[32];
   for (int f = 0; f <= nb; ++f) {
     const int t = b0 + f;
-    const float* in = xf + ((long long)c * T + t) * xs;
+    const float* in = STAGED ? stage : xf + ((long long)c * T + t) * xs;
+    if (STAGED) ptx::mbar_wait(bar, (uint32_t)(f & 1));
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
       const int k = lane + 32 * j;
-      float2 xk = __ldg(reinterpret_cast<const float2*>(in + 2 * k));
-      float2 xm = __ldg(reinterpret_cast<const float2*>(in + 2 * (kM - k)));
+      float2 xk, xm;
+      if (STAGED) {
+        xk = *reinterpret_cast<const float2*>(in + 2 * k);
+        xm = *reinterpret_cast<const float2*>(in + 2 * (kM - k));
+      } else {
+        xk = __ldg(reinterpret_cast<const float2*>(in + 2 * k));
+        xm = __ldg(reinterpret_cast<const float2*>(in + 2 * (kM - k)));
+      }
       if (k == 0) { xk.y = 0.f; xm.y = 0.f; }
       const float2 e = make_float2(0.5f * (xk.x + xm.x), 0.5f * (xk.y - xm.y));
       const float2 dlt = make_float2(0.5f * (xk.x - xm.x), 0.5f * (xk.y + xm.y));
@@ -255,7 +285,14 @@ istft_warp_kernel(const float* __restrict__ xf, int xs, int T, int nseg, int nwo
       const float2 o = cmul(dlt, w);
       v[j] = make_float2(e.x - o.y, e.y + o.x);
     }
-    warp_fft1024<true>(v, tr_all[warp], tw, lane);
+    if (STAGED) {
+      __syncwarp();                                        // every lane has read the staged row
+      if (f < nb && lane == 0) {
+        ptx::mbar_arrive_expect_tx(bar, kStageFloats * 4);
+        ptx::bulk_g2s(ptx::smem_u32(stage), xf + ((long long)c * T + t + 1) * xs, kStageFloats * 4, bar);
+      }
+    }
+    warp_fft1024<true>(v, tr, tw, lane);
     // v[br5(k2)] / 1024 = (x[2n], x[2n+1]), n = lane + 32 k2; k2 < 16 is the first half of the frame
     if (f > 0) {
       float* o = wav + (long long)c * out_len + (long long)(t - 1) * kHop;
@@ -380,7 +417,7 @@ from_frames_kernel(const float* __restrict__ xf, int xs, int T, float* __restric
 // constant tables (per device, created on first use; tiny, live for the process lifetime)
 struct Tables {
   float* window = nullptr;   // [2048]
-  float2* tw = nullptr;      // [1024] W_1024^k, then [1025] W_2048^k
+  float2* tw = nullptr;      // [1024] W_1024^k, then [1025] W_2048^k, then [32][32] W_1024^(l k1) at [k1][l]
 };
 std::mutex g_tab_mu;
 Tables g_tab[64];
@@ -396,9 +433,12 @@ cudaError_t ensure_tables(Tables** out) {
     const double pi = 3.14159265358979323846;
     std::vector<float> w(kN);
     for (int n = 0; n < kN; ++n) w[n] = (float)(0.5 - 0.5 * std::cos(2.0 * pi * n / kN));
-    std::vector<float2> tw(kM + kM + 1);
+    std::vector<float2> tw(kM + kM + 1 + 1024);
     for (int k = 0; k < kM; ++k) tw[k] = make_float2((float)std::cos(2.0 * pi * k / kM), (float)-std::sin(2.0 * pi * k / kM));
     for (int k = 0; k <= kM; ++k) tw[kM + k] = make_float2((float)std::cos(2.0 * pi * k / kN), (float)-std::sin(2.0 * pi * k / kN));
+    for (int k1 = 0; k1 < 32; ++k1)
+      for (int l = 0; l < 32; ++l)
+        tw[kTw32 + k1 * 32 + l] = make_float2((float)std::cos(2.0 * pi * (l * k1) / kM), (float)-std::sin(2.0 * pi * (l * k1) / kM));
     float* dw = nullptr;
     float2* dt = nullptr;
     if ((e = cudaMalloc(&dw, w.size() * sizeof(float))) != cudaSuccess) return e;
@@ -449,16 +489,31 @@ cudaError_t launch_istft_frames(const float* xf, int xs, int C, int T, const flo
   if (T < 2) return cudaSuccess;
   BSB_TABLES(window, tw);
   // a warp walks `per` consecutive output blocks (one extra frame of overlap per warp). Sized so
-  // that all warps are resident at once (148 SMs x 16 warps) when the input allows it: one
+  // that all warps are resident at once (148 SMs x 12 or 16 warps) when the input allows it: one
   // balanced wave and <= 1/per redundant transforms.
+  const bool staged = (xs % 4) == 0 && xs >= kStageFloats && (reinterpret_cast<uintptr_t>(xf) & 15) == 0;
+  const int resident = 148 * kFrameWarps * (staged ? 3 : 4);
   const long long blocks = (long long)C * (T - 1);
-  int per = (int)((blocks + 148 * 16 - 1) / (148 * 16));
+  int per = (int)((blocks + resident - 1) / resident);
   if (per < 1) per = 1;
   if (per > 32) per = 32;
   const int nseg = (T - 1 + per - 1) / per;
   const int nwork = C * nseg;
-  istft_warp_kernel<<<(nwork + kFrameWarps - 1) / kFrameWarps, kFrameWarps * 32, 0, s>>>(xf, xs, T, nseg, nwork, window, tw,
-                                                                                      wav, per);
+  const int grid = (nwork + kFrameWarps - 1) / kFrameWarps;
+  if (staged) {
+    constexpr int smem = kFrameWarps * kIstftWarpSmem;
+    static bool attr_set[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+      cudaError_t e = cudaFuncSetAttribute(istft_warp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      if (e != cudaSuccess) return e;
+      attr_set[dev] = true;
+    }
+    istft_warp_kernel<true><<<grid, kFrameWarps * 32, smem, s>>>(xf, xs, T, nseg, nwork, window, tw, wav, per);
+  } else {
+    istft_warp_kernel<false><<<grid, kFrameWarps * 32, kFrameWarps * 32 * kTr * 8, s>>>(xf, xs, T, nseg, nwork, window, tw, wav, per);
+  }
   count_launch();
   return cudaGetLastError();
 }

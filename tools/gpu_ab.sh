@@ -1,5 +1,5 @@
 timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-for v in "BSB_X=1" "BSB_PAIR=1"; do
+for v in "BSB_X=1"; do
   env $v timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-streaming > gpurun_out/bab.log 2> gpurun_out/bab.err || tail -5 gpurun_out/bab.err
   python - <<PY
 import json
