@@ -238,6 +238,17 @@ istft_warp_kernel(const float* __restrict__ xf, int xs, int T, int nseg, int nwo
                   const float2* __restrict__ tw, float* __restrict__ wav, int per) {
   extern __shared__ __align__(16) uint8_t istft_smem[];
   __shared__ __align__(8) uint64_t bar_all[kFrameWarps];
+  // 1 / (w[i]^2 + w[i+1024]^2) of the overlap-add, once per CTA instead of two loads, an FMA pair and a
+  // reciprocal per output sample (same values: __fdividef(a, b) is a * rcp(b))
+  __shared__ float2 inv_env[kHop / 2];
+  {
+    const float2* wp = reinterpret_cast<const float2*>(win);
+    for (int n = threadIdx.x; n < kHop / 2; n += kFrameWarps * 32) {
+      const float2 w = __ldg(wp + n), u = __ldg(wp + n + kHop / 2);
+      inv_env[n] = make_float2(__fdividef(1.f, fmaf(u.x, u.x, w.x * w.x)), __fdividef(1.f, fmaf(u.y, u.y, w.y * w.y)));
+    }
+  }
+  __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float2* tr = reinterpret_cast<float2*>(istft_smem + (size_t)warp * (STAGED ? kIstftWarpSmem : 32 * kTr * 8));
   const float* stage = reinterpret_cast<const float*>(tr + 32 * kTr);
@@ -248,7 +259,7 @@ istft_warp_kernel(const float* __restrict__ xf, int xs, int T, int nseg, int nwo
   const int nb = min(per, (T - 1) - b0);
   if (nb <= 0) return;
   const long long out_len = (long long)kHop * (T - 1);
-  const float inv_m = 1.0f / kM;
+  const float inv_m = 0.5f / kM;                           // 1/1024 of the inverse FFT and the 1/2 of the split step
   const float2* tw2 = tw + kM;
   const float2* win2 = reinterpret_cast<const float2*>(win);
   if (STAGED) {
@@ -278,11 +289,11 @@ istft_warp_kernel(const float* __restrict__ xf, int xs, int T, int nseg, int nwo
         xm = __ldg(reinterpret_cast<const float2*>(in + 2 * (kM - k)));
       }
       if (k == 0) { xk.y = 0.f; xm.y = 0.f; }
-      const float2 e = make_float2(0.5f * (xk.x + xm.x), 0.5f * (xk.y - xm.y));
-      const float2 dlt = make_float2(0.5f * (xk.x - xm.x), 0.5f * (xk.y + xm.y));
-      float2 w = __ldg(tw2 + k);
-      w.y = -w.y;
-      const float2 o = cmul(dlt, w);
+      // twice the textbook E and O: the factor 1/2 is folded into `scale` below
+      const float2 e = make_float2(xk.x + xm.x, xk.y - xm.y);
+      const float2 dlt = make_float2(xk.x - xm.x, xk.y + xm.y);
+      const float2 w = __ldg(tw2 + k);
+      const float2 o = make_float2(dlt.x * w.x + dlt.y * w.y, dlt.y * w.x - dlt.x * w.y);   // dlt * conj(w)
       v[j] = make_float2(e.x - o.y, e.y + o.x);
     }
     if (STAGED) {
@@ -300,9 +311,9 @@ istft_warp_kernel(const float* __restrict__ xf, int xs, int T, int nseg, int nwo
       for (int k2 = 0; k2 < 16; ++k2) {
         const int n = lane + 32 * k2;
         const float2 z = v[br5(k2)];
-        const float2 w = __ldg(win2 + n), u = __ldg(win2 + n + kHop / 2);
-        const float y0 = __fdividef(fmaf(z.x * inv_m, w.x, prev[k2].x), fmaf(u.x, u.x, w.x * w.x));
-        const float y1 = __fdividef(fmaf(z.y * inv_m, w.y, prev[k2].y), fmaf(u.y, u.y, w.y * w.y));
+        const float2 w = __ldg(win2 + n), r = inv_env[n];
+        const float y0 = fmaf(z.x * inv_m, w.x, prev[k2].x) * r.x;
+        const float y1 = fmaf(z.y * inv_m, w.y, prev[k2].y) * r.y;
         *reinterpret_cast<float2*>(o + 2 * n) = make_float2(y0, y1);
       }
     }
