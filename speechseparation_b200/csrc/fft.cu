@@ -120,6 +120,14 @@ __device__ __forceinline__ float cos32(int m) {   // cos(2 pi m / 32), m = 1..15
 }
 __device__ __forceinline__ float sin32(int m) { return m <= 8 ? cos32(8 - m) : cos32(m - 8); }   // sin x = cos(x - pi/2)
 
+// W_2048^(lane + 32 j) = W_2048^lane * W_64^j: one table load per lane and frame plus compile-time constants instead of
+// 32 table loads (the FFT kernels are limited by L1 bytes per frame, not by FP issue slots).
+__device__ __forceinline__ float2 w64(int j) {   // exp(-2 pi i j / 64), j = 0..31 (folds after unrolling)
+  constexpr float c[32] = {1.0f, 0.995184727f, 0.98078528f, 0.956940336f, 0.923879533f, 0.881921264f, 0.831469612f, 0.773010453f, 0.707106781f, 0.634393284f, 0.555570233f, 0.471396737f, 0.382683432f, 0.290284677f, 0.195090322f, 0.0980171403f, 6.123234e-17f, -0.0980171403f, -0.195090322f, -0.290284677f, -0.382683432f, -0.471396737f, -0.555570233f, -0.634393284f, -0.707106781f, -0.773010453f, -0.831469612f, -0.881921264f, -0.923879533f, -0.956940336f, -0.98078528f, -0.995184727f};
+  constexpr float sn[32] = {0.0f, 0.0980171403f, 0.195090322f, 0.290284677f, 0.382683432f, 0.471396737f, 0.555570233f, 0.634393284f, 0.707106781f, 0.773010453f, 0.831469612f, 0.881921264f, 0.923879533f, 0.956940336f, 0.98078528f, 0.995184727f, 1.0f, 0.995184727f, 0.98078528f, 0.956940336f, 0.923879533f, 0.881921264f, 0.831469612f, 0.773010453f, 0.707106781f, 0.634393284f, 0.555570233f, 0.471396737f, 0.382683432f, 0.290284677f, 0.195090322f, 0.0980171403f};
+  return make_float2(c[j], -sn[j]);
+}
+
 // in-register 32-point DIF FFT; result X[br5(i)] = v[i]. INV: conjugate twiddles, unnormalised.
 template <bool INV>
 __device__ __forceinline__ void fft32(float2 (&v)[32]) {
@@ -206,7 +214,7 @@ stft_warp_kernel(const float* __restrict__ wav, long long L, int T, int nrows, c
   warp_fft1024<false>(v, tr_all[warp], tw, lane);
   // split step: X[k] = E + W2048^k O with Z[k], Z[1024-k]; lane holds k = lane + 32 k2
   float* out = xf + (long long)r * xs;
-  const float2* tw2 = tw + kM;
+  const float2 wl = __ldg(tw + kM + lane);                 // W_2048^lane
   const int partner = (32 - lane) & 31;
 #pragma unroll
   for (int k2 = 0; k2 < 32; ++k2) {
@@ -217,7 +225,7 @@ stft_warp_kernel(const float* __restrict__ wav, long long L, int T, int nrows, c
     const int k = lane + 32 * k2;
     const float2 e = make_float2(0.5f * (zk.x + zm.x), 0.5f * (zk.y - zm.y));
     const float2 o = make_float2(0.5f * (zk.y + zm.y), -0.5f * (zk.x - zm.x));
-    const float2 wo = cmul(__ldg(tw2 + k), o);
+    const float2 wo = cmul(k2 == 0 ? wl : cmul(wl, w64(k2)), o);
     *reinterpret_cast<float2*>(out + 2 * k) = make_float2(e.x + wo.x, e.y + wo.y);
   }
   if (lane == 0) *reinterpret_cast<float2*>(out + 2 * kM) = make_float2(v[0].x - v[0].y, 0.f);
@@ -260,7 +268,7 @@ istft_warp_kernel(const float* __restrict__ xf, int xs, int T, int nseg, int nwo
   if (nb <= 0) return;
   const long long out_len = (long long)kHop * (T - 1);
   const float inv_m = 0.5f / kM;                           // 1/1024 of the inverse FFT and the 1/2 of the split step
-  const float2* tw2 = tw + kM;
+  const float2 wl = __ldg(tw + kM + lane);                 // W_2048^lane
   const float2* win2 = reinterpret_cast<const float2*>(win);
   if (STAGED) {
     if (lane == 0) {
@@ -292,7 +300,7 @@ istft_warp_kernel(const float* __restrict__ xf, int xs, int T, int nseg, int nwo
       // twice the textbook E and O: the factor 1/2 is folded into `scale` below
       const float2 e = make_float2(xk.x + xm.x, xk.y - xm.y);
       const float2 dlt = make_float2(xk.x - xm.x, xk.y + xm.y);
-      const float2 w = __ldg(tw2 + k);
+      const float2 w = j == 0 ? wl : cmul(wl, w64(j));   // W_2048^k
       const float2 o = make_float2(dlt.x * w.x + dlt.y * w.y, dlt.y * w.x - dlt.x * w.y);   // dlt * conj(w)
       v[j] = make_float2(e.x - o.y, e.y + o.x);
     }
