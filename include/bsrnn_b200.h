@@ -128,7 +128,22 @@ int bsb_decode_mask(const float* feat, const float* residual, const float* xf, i
 int bsb_stream_step(const float* chunk, int C, const float* window, const void* packed,
                     float* ring, const float* state, float* new_state, float* tail,
                     float* out, void* ws, size_t ws_bytes, void* stream);
+/* same hop with the LADSPA plugin's dry/wet control applied to the spectrum before synthesis
+ * (speech-ladspa-onnx.cpp:215-226): mix = *DEVICE* float (NULL = the plain step); with X the analysed
+ * spectrum of the hop and Y the model output, mix >= 0 -> mix*Y + (1-mix)*X, mix < 0 -> X + mix*Y. */
+int bsb_stream_step_mix(const float* chunk, int C, const float* window, const void* packed,
+                        float* ring, const float* state, float* new_state, float* tail,
+                        float* out, const float* mix, void* ws, size_t ws_bytes, void* stream);
 size_t bsb_stream_workspace_bytes(int C);
+
+/* --- evaluation sums (m_dataset.train_infer, m_dataset.py:202-226) ---------------------------------
+ * One pass over an (estimate, reference) pair of [rows][n] fp32 arrays (row strides in floats, >= n):
+ *   stats[row][0..4] (DEVICE double, zeroed by the call) =
+ *     sum|e-r|, sum r^2, sum (e-r)^2, sum e*r, sum e^2.
+ * L1 (time, Re, Im), SDR and SI-SDR of train_infer are closed forms of these sums
+ * (speechseparation_b200/wrap.py eval_metrics). rows <= 65535. */
+int bsb_pair_stats(const float* est, long long est_stride, const float* ref, long long ref_stride,
+                   int rows, long long n, double* stats, void* stream);
 
 /* --- measurement -----------------------------------------------------------------------------
  * When enabled, the orchestration functions record CUDA events on `stream` between their

@@ -386,6 +386,44 @@ def stream(sd, wav: torch.Tensor, state: Optional[torch.Tensor] = None):
     return torch.cat(outs, 1), state
 
 
+def plugin_run(sd, left: torch.Tensor, mix: float = 1.0):
+    """The LADSPA plugin's signal path, speech-ladspa-onnx.cpp:174-267, minus FFTW/onnxruntime.
+
+    left [n] = the samples of port "Input (Left)" (the right input is read into a buffer nobody uses,
+    :178,199-203). Returns (out [n], state): what the plugin writes to BOTH output ports.
+      * run() hands out the result of hop k-1 while it collects the samples of hop k (:176-183),
+        so the output is zero for the first 1024 samples and a trailing partial chunk runs no hop;
+      * every model row carries the spectrum of input L (:199-220);
+      * control port: mix >= 0 -> mix*Y + (1-mix)*X, mix < 0 -> X + mix*Y on the spectrum (:215-226);
+      * row 0 of the model output only (:217-218), Hermitian completion + backward FFT / 2048
+        (:229-247), 2-frame overlap-add divided by the two window values (:250-262; no synthesis window).
+    """
+    n = left.shape[0]
+    win = hann()
+    buf = torch.zeros(2, N_FFT)
+    prev = torch.zeros(N_FFT)
+    state = torch.zeros(4, 2, 2 * N_BANDS, FEAT)
+    sum_w = win[:HOP] + win[HOP:]
+    out = torch.zeros(n)
+    for h in range(n // HOP):
+        chunk = left[h * HOP:(h + 1) * HOP]
+        buf = torch.cat((buf[:, HOP:], chunk.expand(2, -1)), 1)
+        spec = torch.fft.rfft(buf[0] * win)
+        x = torch.stack((spec.real, spec.imag), dim=1).reshape(1, -1).repeat(2, 1)
+        y, state = forward_recurrent(sd, x, state)
+        y0 = y[0].reshape(-1, 2)
+        wet = torch.complex(y0[:, 0].contiguous(), y0[:, 1].contiguous())
+        mixed = mix * wet + (1.0 - mix) * spec if mix >= 0.0 else spec + mix * wet
+        cur = torch.fft.irfft(mixed, n=N_FFT)
+        res = (cur[:HOP] + prev[HOP:]) / sum_w
+        prev = cur
+        lo = (h + 1) * HOP
+        hi = min(lo + HOP, n)
+        if hi > lo:
+            out[lo:hi] = res[:hi - lo]
+    return out, state
+
+
 # ----------------------------------------------------------------------------------------
 # metrics (m_dataset.py:201-226)
 # ----------------------------------------------------------------------------------------
@@ -406,6 +444,30 @@ def sdr(est: torch.Tensor, ref: torch.Tensor) -> torch.Tensor:
     n2s = (ref.double() ** 2).sum(1) + 1e-9
     n2d = ((est.double() - ref.double()) ** 2).sum(1) + 1e-9
     return 10.0 * torch.log10(n2s / n2d)
+
+
+def train_infer(sd, waveform: torch.Tensor, speech: torch.Tensor):
+    """m_dataset.train_infer with discriminator=None and lossfn=L1Loss(mean) (m_dataset.py:202-226,
+    train.py:54,140), `x.shape[0]` in place of the literal 2 of m_dataset.py:192.
+    Returns (loss, sdr, sdr2, sdr3) as python floats (float64 arithmetic for the reductions)."""
+    spec = stft_pack(waveform)
+    x = forward(sd, spec)
+    x_time = unpack_istft(x)
+    sp_freq = stft_pack(speech)
+    sp_time = speech[:, :x_time.shape[1]]
+    C = x.shape[0]
+    xr, xi = x.reshape(C, -1, 2, x.shape[2])[:, :, 0].double(), x.reshape(C, -1, 2, x.shape[2])[:, :, 1].double()
+    sr, si = (sp_freq.reshape(C, -1, 2, x.shape[2])[:, :, 0].double(),
+              sp_freq.reshape(C, -1, 2, x.shape[2])[:, :, 1].double())
+    loss = (x_time.double() - sp_time.double()).abs().mean() + (xr - sr).abs().mean() + (xi - si).abs().mean()
+    n2s = sp_time.double().square().sum(1) + 1e-9
+    n2d = (x_time.double() - sp_time.double()).square().sum(1) + 1e-9
+    sdr_ = (10 * torch.log10(n2s / n2d)).mean()
+    n2s2 = speech.double().square().sum(1) + 1e-9
+    n2d2 = (speech.double() - waveform.double()).square().sum(1) + 1e-9
+    sdr2 = (10 * torch.log10(n2s2 / n2d2)).mean()
+    sdr3 = si_sdr(x_time, sp_time).mean()
+    return float(loss), float(sdr_), float(sdr2), float(sdr3)
 
 
 def max_rel_err(y: torch.Tensor, y_ref: torch.Tensor) -> float:

@@ -47,7 +47,66 @@ def ref_model(ref, sd):
     return m.eval()
 
 
+def plugin_loop(m, left, mix, blocks):
+    """speech-ladspa-onnx.cpp:174-267 statement by statement around the reference's forward_recurrent:
+    run() with the given block sizes (cycled), new_chunk() with double-precision FFTs like FFTW's
+    fftw_complex, float tensors in and out of the model, float window."""
+    win = (0.5 * (1 - torch.cos(2 * torch.pi * torch.arange(2048, dtype=torch.float64) / 2048))).float()   # :57-59
+    current = torch.zeros(2, 2048)
+    overlap = [torch.zeros(2048), torch.zeros(2048)]
+    state = torch.zeros(4, 2, 24, 64)
+    buf_in = torch.zeros(1024)
+    buf_out = torch.zeros(1024)
+    out = torch.zeros_like(left)
+    pos = lp = i = 0
+    while pos < left.numel():
+        count = min(blocks[i % len(blocks)], left.numel() - pos)
+        i += 1
+        while count > 0:                                               # run(), :174-191
+            n = min(1024 - lp, count)
+            buf_in[lp:lp + n] = left[pos:pos + n]
+            out[pos:pos + n] = buf_out[lp:lp + n]
+            lp += n
+            pos += n
+            count -= n
+            if lp == 1024:                                             # new_chunk(), :193-267
+                current = torch.cat((current[:, 1024:], buf_in.expand(2, -1)), 1)        # :199-210
+                freq = torch.fft.fft((current[0] * win).double())                         # :206-211
+                tin = torch.stack((freq[:1025].real, freq[:1025].imag), 1).reshape(1, -1).float().repeat(2, 1)
+                tout, state = m.forward_recurrent(tin, state)                             # :236 (+ :264 state copy)
+                y = tout[0].reshape(-1, 2).double()
+                wet = torch.complex(y[:, 0].contiguous(), y[:, 1].contiguous())
+                half = freq[:1025]
+                half = mix * wet + (1.0 - mix) * half if mix >= 0.0 else mix * wet + half    # :215-226
+                full = torch.cat((half, half[1:1024].flip(0).conj()))                     # :229-233
+                t = torch.fft.ifft(full).real.float()                                     # :236-247 (real part / fft_size)
+                overlap = [overlap[1], t]
+                s = overlap[0][1024:] + overlap[1][:1024]                                 # :250-258
+                wsum = win[1024:] + win[:1024]
+                buf_out = s / wsum
+                lp = 0
+    return out, state
+
+
+def gen_plugin(m):
+    left, _ = O.synth_audio(1, 6 * 1024 + 200, seed=11)
+    left = left[0]
+    blocks = [300, 1024, 7, 2048, 1500, 64]
+    rec = {"left": left.numpy(), "blocks": np.array(blocks)}
+    for tag, mix in (("wet", 1.0), ("mix04", 0.4), ("neg05", -0.5)):
+        out, state = plugin_loop(m, left, mix, blocks)
+        rec[f"out_{tag}"] = out.numpy()
+        rec[f"state_{tag}"] = state.numpy()
+        rec[f"mix_{tag}"] = np.array([mix], dtype=np.float32)
+    np.savez_compressed(os.path.join(OUT, "plugin_small.npz"), **rec)
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "plugin":      # only (re)write plugin_small.npz
+        torch.set_grad_enabled(False)
+        torch.set_num_threads(1)
+        gen_plugin(ref_model(load_reference(), O.make_state_dict(0)))
+        return
     torch.set_grad_enabled(False)
     torch.set_num_threads(1)                              # fixed reduction order
     os.makedirs(OUT, exist_ok=True)
@@ -177,6 +236,8 @@ def main():
         outs.append(new_samples / sum_of_window)
     np.savez_compressed(os.path.join(OUT, "stream_small.npz"), wav=wavs.numpy(),
                         out=torch.cat(outs, 1).numpy(), state=state.numpy())
+
+    gen_plugin(m)
 
     meta = {"torch": torch.__version__, "numpy": np.__version__, "threads": 1,
             "weights": "oracle.bsrnn_oracle.make_state_dict(0)",

@@ -41,13 +41,32 @@ SIGNATURES = {
     "bsb_rnn_block": (ci, [ci, cfp, ci, ci, vp, cfp, cfp, cfp, vp, csz, vp]),
     "bsb_decode_mask": (ci, [cfp, cfp, cfp, ci, vp, cfp, vp, csz, vp]),
     "bsb_stream_step": (ci, [cfp, ci, cfp, vp, cfp, cfp, cfp, cfp, cfp, vp, csz, vp]),
+    "bsb_stream_step_mix": (ci, [cfp, ci, cfp, vp, cfp, cfp, cfp, cfp, cfp, cfp, vp, csz, vp]),
     "bsb_stream_workspace_bytes": (csz, [ci]),
+    "bsb_pair_stats": (ci, [cfp, cll, cfp, cll, ci, cll, vp, vp]),
     "bsb_set_stage_timing": (ci, [ci]),
     "bsb_stage_count": (ci, []),
     "bsb_stage_name": (C.c_char_p, [ci]),
     "bsb_stage_times": (ci, [C.POINTER(C.c_float), ci]),
     "bsb_launch_count": (cll, []),
     "bsb_set_force_fp32": (ci, [ci]),
+}
+
+# include/bsrnn_b200_plugin.h (host pointers; the LADSPA-shaped streaming host)
+cul, cdb = C.c_ulong, C.c_double
+PLUGIN_SIGNATURES = {
+    "ladspa_descriptor": (vp, [cul]),
+    "bsb_plugin_weight_floats": (cll, []),
+    "bsb_plugin_create": (ci, [C.POINTER(vp), vp, cll, ci]),
+    "bsb_plugin_create_from_file": (ci, [C.POINTER(vp), C.c_char_p, ci]),
+    "bsb_plugin_connect_port": (None, [vp, cul, vp]),
+    "bsb_plugin_run": (ci, [vp, cul]),
+    "bsb_plugin_reset": (ci, [vp]),
+    "bsb_plugin_hops": (cll, [vp]),
+    "bsb_plugin_last_hop_ms": (cdb, [vp]),
+    "bsb_plugin_max_hop_ms": (cdb, [vp]),
+    "bsb_plugin_get_state": (ci, [vp, vp, cll]),
+    "bsb_plugin_destroy": (None, [vp]),
 }
 
 
@@ -64,7 +83,7 @@ def lib() -> C.CDLL:
                 f"{LIB_PATH} not found: the CUDA library is not built and there is no fallback path. "
                 "Run `python -c 'import __graft_entry__ as g; g.build()'` in the repo root.")
         l = C.CDLL(LIB_PATH)
-        for name, (res, args) in SIGNATURES.items():
+        for name, (res, args) in list(SIGNATURES.items()) + list(PLUGIN_SIGNATURES.items()):
             fn = getattr(l, name)
             fn.restype = res
             fn.argtypes = args

@@ -650,9 +650,9 @@ int bsb_separate(const float* wav, int C, long long L, const float* window, cons
   return 0;
 }
 
-int bsb_stream_step(const float* chunk, int C, const float* window, const void* packed, float* ring,
-                    const float* state, float* new_state, float* tail, float* out, void* ws, size_t ws_bytes,
-                    void* stream) {
+int bsb_stream_step_mix(const float* chunk, int C, const float* window, const void* packed, float* ring,
+                        const float* state, float* new_state, float* tail, float* out, const float* mix,
+                        void* ws, size_t ws_bytes, void* stream) {
   if (!chunk || !packed || !ring || !state || !new_state || !tail || !out || C <= 0 || state == new_state)
     return BSB_E_ARG;
   if (!ws) return BSB_E_ARG;
@@ -668,8 +668,24 @@ int bsb_stream_step(const float* chunk, int C, const float* window, const void* 
   CK(launch_stream_analysis(chunk, C, window, ring, x, s));
   mark("analysis", s);
   CKI(run_model(x, kSpec, C, 1, packed, state, new_state, y, kSpec, w, s));
-  CK(launch_stream_synthesis(y, C, window, tail, out, s));
+  CK(launch_stream_synthesis(y, x, mix, C, window, tail, out, s));
   mark("synthesis", s);
+  return 0;
+}
+
+int bsb_stream_step(const float* chunk, int C, const float* window, const void* packed, float* ring,
+                    const float* state, float* new_state, float* tail, float* out, void* ws, size_t ws_bytes,
+                    void* stream) {
+  return bsb_stream_step_mix(chunk, C, window, packed, ring, state, new_state, tail, out, nullptr, ws, ws_bytes,
+                             stream);
+}
+
+int bsb_pair_stats(const float* est, long long est_stride, const float* ref, long long ref_stride, int rows,
+                   long long n, double* stats, void* stream) {
+  if (!est || !ref || !stats || rows <= 0 || rows > 65535 || n <= 0 || est_stride < n || ref_stride < n)
+    return BSB_E_ARG;
+  if ((reinterpret_cast<uintptr_t>(stats) & 7) != 0) return BSB_E_ALIGN;
+  CK(launch_pair_stats(est, est_stride, ref, ref_stride, rows, n, stats, S(stream)));
   return 0;
 }
 

@@ -92,6 +92,29 @@ __device__ __forceinline__ void irfft_split_load(const float* in, const float2* 
   }
 }
 
+// Same with the plugin's dry/wet control applied to the spectrum first (speech-ladspa-onnx.cpp:215-226):
+// mix >= 0: mix*y + (1-mix)*x ; mix < 0: x + mix*y   (x = the analysed spectrum of this hop).
+__device__ __forceinline__ float2 mix_bin(float2 y, float2 x, float mix) {
+  const float a = mix >= 0.f ? 1.f - mix : 1.f;
+  return make_float2(fmaf(mix, y.x, a * x.x), fmaf(mix, y.y, a * x.y));
+}
+__device__ __forceinline__ void irfft_split_load_mix(const float* in, const float* dry, float mix,
+                                                     const float2* __restrict__ tw2, float2* Z) {
+  for (int k = threadIdx.x; k < kM; k += kFftThreads) {
+    float2 xk = mix_bin(*reinterpret_cast<const float2*>(in + 2 * k),
+                        *reinterpret_cast<const float2*>(dry + 2 * k), mix);
+    float2 xm = mix_bin(*reinterpret_cast<const float2*>(in + 2 * (kM - k)),
+                        *reinterpret_cast<const float2*>(dry + 2 * (kM - k)), mix);
+    if (k == 0) { xk.y = 0.f; xm.y = 0.f; }
+    const float2 e = make_float2(0.5f * (xk.x + xm.x), 0.5f * (xk.y - xm.y));
+    const float2 dlt = make_float2(0.5f * (xk.x - xm.x), 0.5f * (xk.y + xm.y));
+    float2 w = __ldg(tw2 + k);
+    w.y = -w.y;
+    const float2 o = cmul(dlt, w);
+    Z[k] = make_float2(e.x - o.y, e.y + o.x);
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 // Offline path: one WARP per frame. 1024 = 32 x 32: every lane runs a 32-point FFT in registers,
 // the warp transposes once through (padded) shared memory, every lane runs a second 32-point
@@ -370,12 +393,14 @@ stream_analysis_kernel(const float* __restrict__ chunk, const float* __restrict_
 }
 
 __global__ void __launch_bounds__(kFftThreads)
-stream_synthesis_kernel(const float* __restrict__ y, const float* __restrict__ win,
-                        const float2* __restrict__ tw, float* __restrict__ tail, float* __restrict__ out) {
+stream_synthesis_kernel(const float* __restrict__ y, const float* __restrict__ dry, const float* __restrict__ mix,
+                        const float* __restrict__ win, const float2* __restrict__ tw, float* __restrict__ tail,
+                        float* __restrict__ out) {
   __shared__ __align__(16) float2 sa[kM];
   __shared__ __align__(16) float2 sb[kM];
   const int c = blockIdx.x;
-  irfft_split_load(y + (long long)c * kSpec, tw + kM, sa);
+  if (mix != nullptr) irfft_split_load_mix(y + (long long)c * kSpec, dry + (long long)c * kSpec, __ldg(mix), tw + kM, sa);
+  else irfft_split_load(y + (long long)c * kSpec, tw + kM, sa);
   __syncthreads();
   const float2* z = fft1024<true>(sa, sb, tw);
   const float inv_m = 1.0f / kM;
@@ -545,10 +570,10 @@ cudaError_t launch_stream_analysis(const float* chunk, int C, const float* windo
   return cudaGetLastError();
 }
 
-cudaError_t launch_stream_synthesis(const float* y, int C, const float* window, float* tail,
-                                    float* out, cudaStream_t s) {
+cudaError_t launch_stream_synthesis(const float* y, const float* dry, const float* mix, int C, const float* window,
+                                    float* tail, float* out, cudaStream_t s) {
   BSB_TABLES(window, tw);
-  stream_synthesis_kernel<<<C, kFftThreads, 0, s>>>(y, window, tw, tail, out);
+  stream_synthesis_kernel<<<C, kFftThreads, 0, s>>>(y, dry, mix, window, tw, tail, out);
   count_launch();
   return cudaGetLastError();
 }

@@ -136,13 +136,19 @@ cudaError_t launch_istft_frames(const float* xf, int xs, int C, int T, const flo
 cudaError_t launch_stream_analysis(const float* chunk, int C, const float* window, float* ring,
                                    float* x, cudaStream_t s);
 // streaming synthesis: cur = irfft(unpack(y)); out = (cur[:1024] + tail) / (w[i]+w[i+1024]); tail = cur[1024:]
-cudaError_t launch_stream_synthesis(const float* y, int C, const float* window, float* tail,
-                                    float* out, cudaStream_t s);
+cudaError_t launch_stream_synthesis(const float* y, const float* dry, const float* mix, int C, const float* window,
+                                    float* tail, float* out, cudaStream_t s);
 // x[C][2050][T] <-> xf[C*T][xs]
 cudaError_t launch_to_frames(const float* x, int C, int T, float* xf, int xs, cudaStream_t s);
 cudaError_t launch_from_frames(const float* xf, int xs, int C, int T, float* x, cudaStream_t s);
 const float* builtin_window(cudaStream_t s, cudaError_t* err);   // device float[2048], periodic Hann
 const float2* twiddle_tables(cudaStream_t s, cudaError_t* err);  // device: [1024] W_1024^k then [1025] W_2048^k
+
+// ------------------------------------------------------------------------------------
+// evaluation sums (m_dataset.py:202-226): stats[rows][5] = sum|e-r|, sum r^2, sum (e-r)^2, sum e r, sum e^2
+// ------------------------------------------------------------------------------------
+cudaError_t launch_pair_stats(const float* est, long long est_stride, const float* ref, long long ref_stride,
+                              int rows, long long n, double* stats, cudaStream_t s);
 
 // ------------------------------------------------------------------------------------
 // weight packing helpers

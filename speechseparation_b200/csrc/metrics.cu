@@ -1,0 +1,76 @@
+// Evaluation sums of the forward-only consumer m_dataset.train_infer (m_dataset.py:202-226):
+// everything that function reports -- L1 in time, L1 of Re and Im, SDR, SI-SDR -- is a function of five sums
+// per row over an (estimate, reference) pair, gathered here in ONE pass over both arrays (HBM-bound: 8 B per
+// element pair, 16-byte loads, fp32 partials per thread, fp64 from the warp level up, one fp64 atomicAdd per
+// quantity per CTA).
+#include "kernels.cuh"
+
+namespace bsb {
+
+constexpr int kStatThreads = 256;
+constexpr int kStatChunk = 16384;        // elements of one row per CTA
+
+__device__ __forceinline__ void stat_acc(float e, float r, float (&a)[5]) {
+  const float d = e - r;
+  a[0] += fabsf(d);          // sum |e - r|
+  a[1] = fmaf(r, r, a[1]);   // sum r^2
+  a[2] = fmaf(d, d, a[2]);   // sum (e - r)^2
+  a[3] = fmaf(e, r, a[3]);   // sum e r
+  a[4] = fmaf(e, e, a[4]);   // sum e^2
+}
+
+__global__ void __launch_bounds__(kStatThreads)
+pair_stats_kernel(const float* __restrict__ est, long long est_stride, const float* __restrict__ ref,
+                  long long ref_stride, long long n, double* __restrict__ stats) {
+  const int row = blockIdx.y;
+  const float* e = est + row * est_stride;
+  const float* r = ref + row * ref_stride;
+  const long long lo = (long long)blockIdx.x * kStatChunk;
+  const long long hi = min(n, lo + kStatChunk);
+  float a[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+  const bool vec = (((reinterpret_cast<uintptr_t>(e + lo) | reinterpret_cast<uintptr_t>(r + lo)) & 15) == 0);
+  if (vec) {
+    const long long nv = (hi - lo) >> 2;
+    const float4* e4 = reinterpret_cast<const float4*>(e + lo);
+    const float4* r4 = reinterpret_cast<const float4*>(r + lo);
+    for (long long i = threadIdx.x; i < nv; i += kStatThreads) {
+      const float4 x = __ldg(e4 + i), y = __ldg(r4 + i);
+      stat_acc(x.x, y.x, a); stat_acc(x.y, y.y, a); stat_acc(x.z, y.z, a); stat_acc(x.w, y.w, a);
+    }
+    for (long long i = lo + (nv << 2) + threadIdx.x; i < hi; i += kStatThreads) stat_acc(e[i], r[i], a);
+  } else {
+    for (long long i = lo + threadIdx.x; i < hi; i += kStatThreads) stat_acc(e[i], r[i], a);
+  }
+  __shared__ double red[kStatThreads / 32][5];
+  double d[5];
+#pragma unroll
+  for (int q = 0; q < 5; ++q) {
+    d[q] = (double)a[q];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) d[q] += __shfl_xor_sync(0xffffffffu, d[q], o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+    for (int q = 0; q < 5; ++q) red[threadIdx.x >> 5][q] = d[q];
+  }
+  __syncthreads();
+  if (threadIdx.x < 5) {
+    double s = 0.0;
+#pragma unroll
+    for (int w = 0; w < kStatThreads / 32; ++w) s += red[w][threadIdx.x];
+    atomicAdd(stats + row * 5 + threadIdx.x, s);
+  }
+}
+
+cudaError_t launch_pair_stats(const float* est, long long est_stride, const float* ref, long long ref_stride,
+                              int rows, long long n, double* stats, cudaStream_t s) {
+  cudaError_t e = cudaMemsetAsync(stats, 0, sizeof(double) * 5 * rows, s);
+  if (e != cudaSuccess) return e;
+  const long long chunks = (n + kStatChunk - 1) / kStatChunk;
+  dim3 grid((unsigned)chunks, (unsigned)rows);
+  pair_stats_kernel<<<grid, kStatThreads, 0, s>>>(est, est_stride, ref, ref_stride, n, stats);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace bsb

@@ -80,6 +80,70 @@ def infer(model: BSRNN, waveform: torch.Tensor, window: Optional[torch.Tensor] =
     return x, unpack_istft(x, window)
 
 
+def pair_stats(est: torch.Tensor, ref: torch.Tensor) -> torch.Tensor:
+    """Per-row sums over an (estimate, reference) pair of float32 CUDA tensors [rows, ...] in ONE pass:
+    returns float64 [rows, 5] = sum|e-r|, sum r^2, sum (e-r)^2, sum e*r, sum e^2 (bsb_pair_stats)."""
+    for t in (est, ref):
+        if not isinstance(t, torch.Tensor) or not t.is_cuda or t.dtype != torch.float32:
+            raise RuntimeError("pair_stats takes float32 CUDA tensors: speechseparation_b200 has no CPU path")
+    if est.shape != ref.shape or est.dim() < 2 or est.device != ref.device:
+        raise RuntimeError(f"pair_stats: shapes/devices differ or no row dimension: {tuple(est.shape)} vs {tuple(ref.shape)}")
+    rows = est.shape[0]
+    e = est.reshape(rows, -1)
+    r = ref.reshape(rows, -1)
+    if e.stride(1) != 1:
+        e = e.contiguous()
+    if r.stride(1) != 1:
+        r = r.contiguous()
+    with torch.cuda.device(est.device):
+        stats = torch.empty((rows, 5), dtype=torch.float64, device=est.device)
+        _lib.check(_lib.lib().bsb_pair_stats(e.data_ptr(), e.stride(0) if rows > 1 else e.shape[1], r.data_ptr(),
+                                             r.stride(0) if rows > 1 else r.shape[1], rows, e.shape[1],
+                                             stats.data_ptr(), _stream_ptr()), "bsb_pair_stats")
+    return stats
+
+
+def metrics_from_stats(stats: torch.Tensor, n: int):
+    """(l1_mean, sdr[rows], si_sdr[rows]) from pair_stats sums; n = elements per row.
+    SDR as m_dataset.py:214-217 (+1e-9 on both energies); SI-SDR as the torchmetrics default the reference
+    uses (m_dataset.py:201,224: zero_mean=False, eps = float32 eps)."""
+    abs_d, rr, dd, er, ee = (stats[:, i] for i in range(5))
+    l1 = abs_d.sum() / (stats.shape[0] * n)
+    sdr = 10.0 * torch.log10((rr + 1e-9) / (dd + 1e-9))
+    eps = torch.finfo(torch.float32).eps
+    alpha = (er + eps) / (rr + eps)
+    tgt = alpha * alpha * rr
+    noise = (tgt - 2.0 * alpha * er + ee).clamp_min(0.0)
+    si = 10.0 * torch.log10((tgt + eps) / (noise + eps))
+    return l1, sdr, si
+
+
+def train_infer(model: BSRNN, sample, window: Optional[torch.Tensor] = None):
+    """Forward-only mirror of m_dataset.train_infer(model, None, sample, L1Loss) (m_dataset.py:202-226), the
+    body of train.py's no_grad validation loop (train.py:132-152): returns (loss, sdr, sdr2, sdr3) as
+    0-dim float64 CUDA tensors. sample = (mixture [C,L], speech [C,L]) float32 CUDA tensors (the reference's
+    leading batch-1 dimension is accepted and squeezed, m_dataset.py:184-185).
+    All reductions run on the device in one pass per pair (no torchmetrics)."""
+    waveform, speech = sample
+    if waveform.dim() == 3:
+        waveform, speech = waveform.squeeze(0), speech.squeeze(0)
+    _check_wav(waveform)
+    _check_wav(speech)
+    x, x_time = infer(model, waveform, window)
+    speech_freq = stft_pack(speech, window)
+    speech_time = speech[:, :x_time.shape[1]]
+    n_t = x_time.shape[1]
+    st_time = pair_stats(x_time, speech_time)
+    st_freq = pair_stats(x, speech_freq)
+    st_mix = pair_stats(waveform, speech)
+    l1_time, sdr, sisdr = metrics_from_stats(st_time, n_t)
+    # L1(Re) + L1(Im): each a mean over C*1025*T elements = the packed array's sum / (C*1025*T)
+    l1_freq = st_freq[:, 0].sum() / (x.shape[0] * (x.shape[1] // 2) * x.shape[2])
+    # sdr2 (m_dataset.py:219-222): n2Delta = |speech - mixture|^2: here the "estimate" is the mixture
+    _, sdr2, _ = metrics_from_stats(st_mix, waveform.shape[1])
+    return l1_time + l1_freq, sdr.mean(), sdr2.mean(), sisdr.mean()
+
+
 class StreamingSeparator:
     """Hop-by-hop separation with carried LSTM state (infer-streaming.py:84-147).
 

@@ -384,3 +384,79 @@ def test_batch_separator_pipeline_equals_separate(dev, model):
         pipe.submit(torch.randn(C, L), outs[0])              # not pinned
     with pytest.raises(RuntimeError):
         pipe.submit(ins[0][:, :-1].contiguous().pin_memory(), outs[0])
+
+
+def test_ladspa_plugin_host_vs_golden_and_oracle(dev, oracle_sd, golden_dir, tmp_path):
+    """The LADSPA-shaped C++ host (csrc/plugin.cpp) against the reference plugin loop (golden) with ragged
+    run() block sizes, three control-port values, graph replay after the second hop, reset, and the
+    descriptor path a LADSPA host takes (instantiate from BSRNN_B200_WEIGHTS)."""
+    from speechseparation_b200 import plugin
+    g = np.load(os.path.join(golden_dir, "plugin_small.npz"))
+    left = g["left"]
+    blocks = [int(b) for b in g["blocks"]]
+    p = plugin.SpeechSeparatorPlugin(oracle_sd, device=dev.index or 0)
+    for tag in ("wet", "mix04", "neg05"):
+        p.reset()
+        out = p.process(left, mix=float(g["mix_" + tag][0]), blocks=blocks)
+        assert rel(torch.from_numpy(out)[None], torch.from_numpy(g["out_" + tag])[None]) < STAGE_TOL, tag
+        assert float((p.state() - torch.from_numpy(g["state_" + tag])).abs().max()) < 1e-4
+    assert p.hops == 18 and 0.0 < p.last_hop_ms <= p.max_hop_ms
+    # block-size independence: one sample at a time == one big block (bit-exact, same kernels)
+    p.reset()
+    a = p.process(left[:3 * 1024 + 5], mix=1.0, blocks=[1])
+    p.reset()
+    b = p.process(left[:3 * 1024 + 5], mix=1.0, blocks=[4096])
+    assert np.array_equal(a, b)
+    p.close()
+    # through ladspa_descriptor(0), as an audio host would
+    wpath = str(tmp_path / "weights.f32")
+    plugin.export_weights(oracle_sd, wpath)
+    os.environ["BSRNN_B200_WEIGHTS"] = wpath
+    os.environ["BSRNN_B200_DEVICE"] = str(dev.index or 0)
+    d = plugin.ladspa_descriptor(0)
+    h = d.instantiate(None, 44100)
+    assert h
+    n = 4 * 1024
+    ctl = np.array([1.0], dtype=np.float32)
+    inp = np.ascontiguousarray(left[:n])
+    o_l, o_r = np.zeros(n, np.float32), np.zeros(n, np.float32)
+    for port, buf in enumerate((ctl, inp, inp, o_l, o_r)):
+        d.connect_port(h, port, buf.ctypes.data)
+    d.run(h, n)
+    d.cleanup(h)
+    ref, _ = O.plugin_run(oracle_sd, torch.from_numpy(inp), 1.0)
+    assert rel(torch.from_numpy(o_l)[None], ref[None]) < STAGE_TOL and np.array_equal(o_l, o_r)
+    del os.environ["BSRNN_B200_WEIGHTS"]
+    assert not d.instantiate(None, 44100)          # no weights configured: NULL handle, message on stderr
+
+
+@pytest.mark.parametrize("rows,n,off", [(1, 1, 0), (2, 4099, 0), (3, 50001, 1), (5, 16384 * 2, 3), (2, 441000, 0)])
+def test_pair_stats_vs_float64(dev, rows, n, off):
+    """bsb_pair_stats against float64 torch sums: ragged lengths, unaligned row starts (strided views), n = 1."""
+    from speechseparation_b200 import pair_stats
+    g = torch.Generator().manual_seed(rows * 131 + n)
+    eb = torch.randn(rows, n + 7, generator=g)
+    rb = torch.randn(rows, n + 7, generator=g) * 0.5 + 0.3 * eb
+    e, r = eb[:, off:off + n], rb[:, off:off + n]
+    st = pair_stats(e.to(dev)[:, :], r.to(dev)[:, :]).cpu()
+    st2 = pair_stats(eb.to(dev)[:, off:off + n], rb.to(dev)[:, off:off + n]).cpu()      # non-contiguous rows, odd offset
+    ed, rd = e.double(), r.double()
+    want = torch.stack(((ed - rd).abs().sum(1), (rd * rd).sum(1), ((ed - rd) ** 2).sum(1), (ed * rd).sum(1),
+                        (ed * ed).sum(1)), 1)
+    scale = torch.stack(((ed - rd).abs().sum(1), (rd * rd).sum(1), ((ed - rd) ** 2).sum(1), (ed * rd).abs().sum(1),
+                         (ed * ed).sum(1)), 1).clamp_min(1e-30)
+    assert float(((st - want).abs() / scale).max()) < 2e-6
+    assert float(((st2 - want).abs() / scale).max()) < 2e-6
+
+
+def test_train_infer_metrics_vs_oracle(dev, model, oracle_sd):
+    """Forward-only m_dataset.train_infer (loss, sdr, sdr2, si-sdr) with every reduction on the device."""
+    from speechseparation_b200 import train_infer
+    wav, src = O.synth_audio(2, 30000, seed=21)
+    want = O.train_infer(oracle_sd, wav, src)
+    got = [float(v) for v in train_infer(model, (wav.to(dev)[None], src.to(dev)[None]))]
+    assert abs(got[0] - want[0]) < 1e-4 * abs(want[0])
+    for a, b in zip(got[1:], want[1:]):
+        assert abs(a - b) < 0.01, (got, want)            # dB
+    with pytest.raises(RuntimeError):
+        train_infer(model, (wav, src))                   # host tensors: no CPU path

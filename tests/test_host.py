@@ -150,3 +150,47 @@ def test_gloo_world2_sharding_and_aggregation():
         assert p.exitcode == 0
     assert [(r[1], r[2]) for r in res] == [(0, 512), (512, 1024)]
     assert all(r[3] == 1024.0 and r[4] == 1.5 for r in res)   # sum of units, max of seconds
+
+
+def test_plugin_header_symbols_and_ladspa_descriptor():
+    """include/bsrnn_b200_plugin.h: every declared function is exported; the LADSPA descriptor carries the
+    reference plugin's identity and port layout (speech-ladspa-onnx.cpp:293-337). No GPU needed."""
+    from speechseparation_b200 import _lib, plugin
+    hdr = open(os.path.join(ROOT, "include", "bsrnn_b200_plugin.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(bsb_plugin_[a-z0-9_]+|ladspa_descriptor)\s*\(", hdr))
+    l = _lib.lib()
+    for name in declared:
+        assert hasattr(l, name), f"{name} declared in the plugin header but not exported"
+    assert declared == set(_lib.PLUGIN_SIGNATURES), declared ^ set(_lib.PLUGIN_SIGNATURES)
+    d = plugin.ladspa_descriptor(0)
+    assert plugin.ladspa_descriptor(1) is None
+    assert d.UniqueID == 0xf433b044 and d.Label == b"speech_separator" and d.PortCount == 5 and d.Properties == 0
+    assert [d.PortDescriptors[i] for i in range(5)] == [0x1 | 0x4, 0x1 | 0x8, 0x1 | 0x8, 0x2 | 0x8, 0x2 | 0x8]
+    assert [d.PortNames[i] for i in range(5)] == [b"Control", b"Input (Left)", b"Input (Right)", b"Output (Left)",
+                                                  b"Output (Right)"]
+    assert d.PortRangeHints[0].HintDescriptor == (0x240 | 0x1) and d.PortRangeHints[0].LowerBound == 0.0
+    assert all(d.PortRangeHints[i].HintDescriptor == 0 for i in range(1, 5))
+    assert not d.activate and not d.run_adding and not d.deactivate
+    assert d.instantiate and d.connect_port and d.run and d.cleanup
+    assert l.bsb_plugin_weight_floats() == 7481062
+
+
+def test_plugin_argument_errors_and_weight_file(tmp_path, oracle_sd):
+    from speechseparation_b200 import _lib, plugin
+    l = _lib.lib()
+    h = ctypes.c_void_p()
+    assert l.bsb_plugin_create(ctypes.byref(h), None, 7481062, 0) == -1 and not h
+    w = plugin.flat_weights(oracle_sd)
+    assert w.size == 7481062 and w.dtype.name == "float32"
+    assert l.bsb_plugin_create(ctypes.byref(h), w.ctypes.data, 10, 0) == -1 and not h
+    assert l.bsb_plugin_run(None, 4) == -1 and l.bsb_plugin_hops(None) == -1
+    short = tmp_path / "short.bin"
+    w[:100].tofile(short)
+    assert l.bsb_plugin_create_from_file(ctypes.byref(h), str(short).encode(), 0) == -2      # wrong size: shape error
+    assert l.bsb_plugin_create_from_file(ctypes.byref(h), b"/nonexistent/w.bin", 0) == -1
+    # flat image = state_dict order
+    first = next(iter(oracle_sd.values())).reshape(-1).numpy()
+    assert (w[:first.size] == first).all()
+    with pytest.raises(RuntimeError):
+        plugin.flat_weights({"a": torch.zeros(3)})

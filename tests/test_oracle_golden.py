@@ -139,3 +139,18 @@ def test_oracle_vs_imported_reference(oracle_sd):
     yr, sr = m.forward_recurrent(x[:, :, 0], st)
     yo, so = O.forward_recurrent(oracle_sd, x[:, :, 0], st)
     assert O.max_rel_err(yo, yr) < TOL and float((so - sr).abs().max()) < TOL
+
+
+def test_plugin_oracle_vs_reference_plugin_loop(golden_dir, oracle_sd):
+    """oracle.plugin_run (block-size independent restatement) against the statement-by-statement plugin loop
+    run around the reference model with ragged run() block sizes (oracle/gen_golden.py plugin_loop)."""
+    g = np.load(os.path.join(golden_dir, "plugin_small.npz"))
+    left = torch.from_numpy(g["left"])
+    for tag in ("wet", "mix04", "neg05"):
+        out, state = O.plugin_run(oracle_sd, left, float(g["mix_" + tag][0]))
+        assert O.max_rel_err(out[None], torch.from_numpy(g["out_" + tag])[None]) < 1e-5
+        assert float((state - torch.from_numpy(g["state_" + tag])).abs().max()) < 1e-5
+    # first hop of output is silence, a dry mix is the input delayed by two hops (FIFO + frame overlap)
+    dry, _ = O.plugin_run(oracle_sd, left, 0.0)
+    assert float(dry[:1024].abs().max()) == 0.0
+    assert float((dry[2048:6 * 1024] - left[:4 * 1024]).abs().max()) < 1e-6
