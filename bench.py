@@ -54,9 +54,11 @@ GEMM = "tc_grouped_linear_kernel"
 STAGE_KERNEL = {"stft": ("stft_warp_kernel", 1), "istft": ("istft_warp_kernel", 1), "pre": (GEMM, 2), "bandfc": (GEMM, 3),
                 "back": (GEMM, 3), "post_mask": (GEMM, 2)}
 for _j in range(4):
-    _k = "lstm_tc_kernel" if _j % 2 == 0 else "lstm_seq_kernel"
-    STAGE_KERNEL[f"rnn{_j}.rec0"] = (_k, 1)
-    STAGE_KERNEL[f"rnn{_j}.rec1"] = (_k, 1)
+    if _j % 2 == 0:
+        STAGE_KERNEL[f"rnn{_j}.rec0"] = ("lstm_tc_kernel", 1)
+        STAGE_KERNEL[f"rnn{_j}.rec1"] = ("lstm_tc_kernel", 1)
+    else:                                   # both time-axis layers run in one launch (lstm_seq2.cu)
+        STAGE_KERNEL[f"rnn{_j}.rec"] = ("lstm_seq2_kernel", 1)
     STAGE_KERNEL[f"rnn{_j}.fc"] = (GEMM, 1)
 
 
@@ -74,6 +76,8 @@ def stage_work(T: int):
         mac[f"rnn{j}.rec0"] = 12 * (64 * 64 + 64 * 256 * nd + 64 * 256 * nd)
         mac[f"rnn{j}.rec1"] = 12 * (64 * nd * 256 * nd + 64 * 256 * nd)
         mac[f"rnn{j}.fc"] = 12 * (64 * nd * 64)
+    for j in (1, 3):
+        mac[f"rnn{j}.rec"] = mac.pop(f"rnn{j}.rec0") + mac.pop(f"rnn{j}.rec1")
     flops = {k: 2.0 * v for k, v in mac.items()}
     flops["stft"] = flops["istft"] = 5.0 * 1024 * 10 + 8 * 1024      # 1024-pt complex FFT + split
     byt = {"stft": 4096 + 8200, "istft": 8200 + 4096, "pre": 8200 + 8200, "bandfc": 8200 + 3072,
@@ -83,6 +87,8 @@ def stage_work(T: int):
         byt[f"rnn{j}.rec0"] = 3072 + 12 * 64 * nd * 4
         byt[f"rnn{j}.rec1"] = 12 * 64 * nd * 4 * 2
         byt[f"rnn{j}.fc"] = 12 * 64 * nd * 4 + 3072 * 2
+    for j in (1, 3):
+        byt[f"rnn{j}.rec"] = byt.pop(f"rnn{j}.rec0") + byt.pop(f"rnn{j}.rec1")
     return flops, byt
 
 
@@ -392,11 +398,12 @@ def main():
                for n_, v in kern.items()}
     # serial depth of the time-axis recurrence: device time of one layer / its T steps
     rec_us = None
-    if "rnn1.rec0" in stage_ms:
-        rec_us = {"time_axis_us_per_step": 1e3 * stage_ms["rnn1.rec0"] / T,
+    if "rnn1.rec" in stage_ms:
+        rec_us = {"time_axis_us_per_step": 1e3 * stage_ms["rnn1.rec"] / T,
                   "band_axis_us_per_step_per_tile": 1e3 * stage_ms["rnn0.rec0"] / 12 / max(1, -(-(2 * -(-frame_rows // 128)) // 148)),
-                  "note": "time axis: one lstm_seq_kernel layer / T steps (8 sequences per CTA); band axis: one lstm_tc_kernel "
-                          "layer / 12 steps / waves of 128-sequence tiles over 148 SMs"}
+                  "note": "time axis: one lstm_seq2_kernel launch (BOTH layers of a block as a wavefront, 16 sequences per "
+                          "CTA) / T steps; band axis: one lstm_tc_kernel layer / 12 steps / waves of 128-sequence tiles "
+                          "over 148 SMs"}
     res = {
         "metric": "audio-sec separated/sec", "value": units / tmax, "unit": "audio-sec/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tmax / args.steps,

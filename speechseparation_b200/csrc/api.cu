@@ -1,6 +1,7 @@
 // C ABI of libbsrnn_b200.so (include/bsrnn_b200.h): argument checks, workspace carving and the
 // stage-by-stage orchestration of the kernels in linear.cu / lstm.cu / fft.cu.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 #include "../../include/bsrnn_b200.h"
@@ -384,7 +385,26 @@ int run_rnn_block(int j, const float* fin, int C, int T, const void* packed, con
   if (!band && T >= kLstmSeqMinSteps && !force_ffma()) {
     // latency path: 8 sequences per CTA, fc_in and W_ih fused into the recurrence (lstm_seq.cu)
     float* hl[2] = {w.hbuf, w.xproj};
-    for (int layer = 0; layer < 2; ++layer) {
+    static const bool one_layer_launches = std::getenv("BSB_SEQ1") != nullptr;     // A/B switch: lstm_seq.cu
+    if (!one_layer_launches) {
+      LstmSeq2Args a{};
+      a.x = fin; a.hmid = hl[0]; a.hout = hl[1];
+      a.nseq = C * kBands; a.nsteps = T; a.n_inner = kBands;
+      a.outer = (long long)T * kBands * kFeat; a.inner = kFeat; a.step = (long long)kBands * kFeat;
+      const long long per = (long long)a.nseq * kFeat;       // state [2(h,c)][2 layers][nseq][64]
+      for (int layer = 0; layer < 2; ++layer) {
+        a.wfrag[layer] = PW(packed, R.sqw[layer]);
+        a.bias[layer] = PW(packed, R.sqb[layer]);
+        if (st_in) { a.h0[layer] = st_in + layer * per; a.c0[layer] = st_in + (2 + layer) * per; }
+        if (st_out) { a.hN[layer] = st_out + layer * per; a.cN[layer] = st_out + (2 + layer) * per; }
+      }
+      if (rows >= kTcMinRows) { a.hplanes = w.planeA; a.hp_lo = kPlaneBlock; }
+      a.flags = reinterpret_cast<int*>(w.t64);                // t64 is only used by the FFMA fallback path
+      CK(launch_lstm_seq2(a, s));
+      std::snprintf(nm, sizeof(nm), "rnn%d.rec", j);
+      mark(nm, s);
+    }
+    for (int layer = 0; one_layer_launches && layer < 2; ++layer) {
       LstmSeqArgs a{};
       a.x = layer == 0 ? fin : hl[0];
       a.hout = hl[layer];

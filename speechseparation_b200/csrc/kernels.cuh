@@ -119,6 +119,27 @@ struct LstmSeqArgs {
   long long hp_lo;
 };
 cudaError_t launch_lstm_seq(const LstmSeqArgs& a, cudaStream_t s);
+// Both layers of a time-axis block in ONE launch, 16 sequences per group, layer 1 a few steps behind layer 0
+// (lstm_seq2.cu). x, hmid (layer-0 output = layer-1 input) and hout share one addressing:
+// (seq / n_inner) * outer + (seq % n_inner) * inner + step * step.
+struct LstmSeq2Args {
+  const float* x;
+  float* hmid;
+  float* hout;
+  const void* wfrag[2];      // per layer: layout.h RnnBlock::sqw
+  const float* bias[2];      // RnnBlock::sqb
+  const float* h0[2];        // optional initial state [nseq][64] per layer
+  const float* c0[2];
+  float* hN[2];              // optional final state
+  float* cN[2];
+  long long outer, inner, step;
+  int n_inner, nseq, nsteps;
+  void* hplanes;             // optional: layer-1 h as bf16 hi/lo planes instead of fp32 rows at hout
+  long long hp_lo;
+  int* flags;                // [ceil(nseq / 16)] ints of scratch (zeroed by the launch)
+  int exp;                   // experiment switches (BSB_SEQ2_EXP), 0 in production
+};
+cudaError_t launch_lstm_seq2(const LstmSeq2Args& a, cudaStream_t s);
 constexpr int kLstmSeqMinSteps = 2;  // single steps (streaming hops) stay on the FFMA recurrence
 constexpr int kLstmTcMinSeq = 128;   // below one full tile the FFMA recurrence is used
 int force_ffma();

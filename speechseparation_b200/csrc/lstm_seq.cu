@@ -82,7 +82,7 @@ lstm_seq_kernel(const __grid_constant__ LstmSeqArgs a) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(16) __nv_bfloat16 hB[2][2][SQ][BS];   // [buffer][plane][sequence][k]
   __shared__ __align__(16) float hF[2][SQ][FS];
-  __shared__ __align__(8) uint64_t bar_xfull[2], bar_xempty[2], bar_accfull[2], bar_accfree[2], bar_ringfull[2], bar_ringfree[2];
+  __shared__ __align__(8) uint64_t bar_xfull[2], bar_xempty[2], bar_accfull[2], bar_accfree[2], bar_ringfull[2], bar_ringfree[4];
   __shared__ uint32_t tmem_slot;
 
   const int tid = threadIdx.x;
@@ -100,8 +100,8 @@ lstm_seq_kernel(const __grid_constant__ LstmSeqArgs a) {
       mbar_init(smem_u32(&bar_accfull[i]), 1);
       mbar_init(smem_u32(&bar_accfree[i]), N_HELP * 32);
       mbar_init(smem_u32(&bar_ringfull[i]), 32);
-      mbar_init(smem_u32(&bar_ringfree[i]), NWARP);
     }
+    for (int i = 0; i < 4; ++i) mbar_init(smem_u32(&bar_ringfree[i]), NWARP);
     fence_mbar_init();
   }
   if (w == MMA_WARP) {
@@ -177,7 +177,7 @@ lstm_seq_kernel(const __grid_constant__ LstmSeqArgs a) {
       float acc[4] = {xlo.x + b_lo, xlo.y + b_lo, xhi.x + b_hi, xhi.y + b_hi};
       if ((t & 3) == 3 || t == a.nsteps - 1) {       // this warp has read its last value of the ring half
         __syncwarp();
-        if (lane == 0) mbar_arrive(smem_u32(&bar_ringfree[(t >> 2) & 1]));
+        if (lane == 0) mbar_arrive(smem_u32(&bar_ringfree[(t >> 2) & 3]));
       }
       matpart(acc, wh, hB[cur], gr, tq);
       const float s0 = odd ? acc[0] : acc[1], s1 = odd ? acc[2] : acc[3];
@@ -258,7 +258,6 @@ lstm_seq_kernel(const __grid_constant__ LstmSeqArgs a) {
     };
     const uint32_t tlane = tmem_base + ((uint32_t)(dq * 32) << 16);
     uint8_t* ring_w = smem_gen + OFF_RING + (lane >> 3) * STEP_STRIDE + (lane & 7) * 4;   // (step in quarter, sequence)
-    int ring_seen = 0;     // completions of bar_ringfree[dq & 1] this warp has observed (a parity wait may lag one phase at most)
     load_block(0);
     for (int b = 0; b < nblk; ++b) {
       if (b + 1 < nblk) {
@@ -269,9 +268,11 @@ lstm_seq_kernel(const __grid_constant__ LstmSeqArgs a) {
       if (g < nq) {
         mbar_wait(smem_u32(&bar_accfull[b & 1]), (b >> 1) & 1);
         tc_fence_after();
-        // quarter g-2 (the previous user of this ring half, written by the other warp of the half) is consumed:
-        // that is completion (g >> 1) - 1 of the barrier; every completion is observed in order
-        for (; ring_seen < (g >> 1); ++ring_seen) mbar_wait(smem_u32(&bar_ringfree[g & 1]), ring_seen & 1);
+        // quarter g-2 (the previous user of this ring half, written by warp dq ^ 2) must be consumed. One free
+        // barrier per helper warp's quarters (index = quarter % 4), each waited on by exactly one warp (this one
+        // waits on dq ^ 2): a completion can never run two phases ahead of its only observer, however long the
+        // observer was held up elsewhere (e.g. waiting for the other layer's rows).
+        if (g >= 2) mbar_wait(smem_u32(&bar_ringfree[dq ^ 2]), (uint32_t)(((g - 2) >> 2) & 1));
         uint8_t* dst = ring_w + (g & 1) * HALF_BYTES;
 #pragma unroll 1
         for (int cb = 0; cb < kGates / 32; ++cb) {

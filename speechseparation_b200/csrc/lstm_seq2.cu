@@ -1,0 +1,429 @@
+// Time-axis LSTM block, BOTH layers in one launch, every matrix product on tcgen05 (TimewiseLSTM,
+// bsrnn.py:101-128; nn.LSTM semantics bsrnn.py:70).
+//
+// The step count T is the serial depth of this part of the model. Two things shorten it:
+//
+// 1. Wavefront over the layers: CTA 2g advances layer 0 of sequence group g (16 sequences), CTA 2g+1 advances
+//    layer 1 of the same group a few steps behind it, reading layer 0's h rows from L2 as they are published
+//    (one release flag per group, bumped every 4 steps). Depth T + lag instead of 2T.
+//
+// 2. The recurrent product itself runs TRANSPOSED on the 5th-gen tensor core:
+//      gates^T[256 gate rows x 16 sequences] = W_ih' . x_t^T + W_hh . h_{t-1}^T
+//    as two M = 128 tiles with N = 16, the weights (bf16 hi/lo) resident in TENSOR MEMORY as the A operand
+//    (TS form: 256 of the 512 columns), x and h as small K-major B operands in shared memory. The warp-level
+//    MMA this replaces costs ~20 cycles per m16n8k16 per SM sub-partition on this part (measured with a
+//    clock trace): 1,900 cycles per step for 16 sequences, against a few hundred for the 24 tcgen05.mma here.
+//    * W_ih'.x runs one block (4 steps x 16 sequences = 64 accumulator columns per tile) ahead, off the serial
+//      path: issued right after the recurrent MMAs of the last step of the previous block, it executes while
+//      the cell update of that step is computed.
+//    * W_hh.h_{t-1} accumulates ONTO the 16 columns of step t, so the accumulator holds the complete
+//      pre-activations. The gate rows are permuted so that the 16 rows cell-warp w needs sit in the TMEM lanes
+//      it may read (32 (w % 4) + 16 ((w / 4) % 2), tile w / 8); tcgen05.ld.16x256b returns the m16n8 fragment
+//      layout (tools/tmem16_probe.cu), i.e. lane pairs (l, l ^ 4) hold i,g / f,o of one (unit, sequence) cell
+//      exactly as the packed gate order (pack.cu seq_row_of) was built for.
+//    Per step: [MMA warp] wait h_{t-1} -> 24 MMAs -> commit | [16 cell warps] wait -> tcgen05.ld -> cell update
+//    (ex2/rcp) -> h_t as bf16 hi/lo into the swizzled B operand -> fence.proxy.async -> arrive. No block-wide
+//    barrier inside the loop.
+//
+//   warps 0-15  cell update (one (unit, sequence) cell per lane and n8 half), h flush (fp32 rows or bf16 planes)
+//   warps 16-19 weights -> TMEM once; x rows (global/L2) -> swizzled bf16 hi/lo B operand, 4 blocks ahead
+//   warp  20    tcgen05 issuer
+#include <cstdlib>
+#include "kernels.cuh"
+#include "ptx.cuh"
+
+namespace bsb {
+namespace {
+
+using namespace ptx;
+
+constexpr int SQ = 16;           // sequences per CTA (N of the recurrent MMA)
+constexpr int TS = 8;            // sequences per accumulator fragment
+constexpr int NWARP = 16;        // cell warps
+constexpr int NT = NWARP * 32;
+constexpr int HELP_WARP0 = NWARP, N_HELP = 4, MMA_WARP = NWARP + N_HELP;
+constexpr int THREADS = (MMA_WARP + 1) * 32;
+constexpr int FS = 68;           // fp32 row stride of the h staging buffers
+constexpr int BLK = 4;           // steps per projection block (4 steps x 16 sequences = 64 columns per tile)
+constexpr int NXB = 4;           // x-block buffers in shared memory
+constexpr int X_PLANE = BLK * SQ * 128;               // 8 KB: [64 (step, sequence) rows][64 k] bf16
+constexpr int H_PLANE = SQ * 128;                     // 2 KB: [16 sequences][64 k] bf16
+constexpr int OFF_X = 0, OFF_H = NXB * 2 * X_PLANE;
+constexpr int SMEM_BYTES = OFF_H + 2 * H_PLANE + 1024;
+// tensor memory columns
+constexpr int COL_ACC = 0;       // [2 buffers][2 tiles][BLK steps][16 sequences] fp32
+constexpr int COL_WIH = 256;     // [2 tiles][2 planes][32]: lane = gate row, column = two consecutive k (bf16)
+constexpr int COL_WHH = 384;
+
+// 16 TMEM lanes x 8 columns -> the m16n8 accumulator fragment (rows lane/4, lane/4 + 8; columns 2 (lane % 4), +1)
+__device__ __forceinline__ void tmem_ld_frag(uint32_t taddr, float (&r)[4]) {
+  asm volatile("tcgen05.ld.sync.aligned.16x256b.x1.b32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(r[0]), "=f"(r[1]), "=f"(r[2]), "=f"(r[3]) : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait_frag2(float (&r)[4], float (&q)[4]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+f"(r[0]), "+f"(r[1]), "+f"(r[2]), "+f"(r[3]), "+f"(q[0]), "+f"(q[1]), "+f"(q[2]), "+f"(q[3]) : : "memory");
+}
+
+#ifdef BSB_SEQ2_TRACE
+// timeline of cell warp 0 and the MMA warp of CTAs 0 and 1 over steps [kTr0, kTr0 + kTrN)
+constexpr int kTr0 = 200, kTrN = 8, kTrP = 8;
+__device__ long long g_seq2_trace[2][2][kTrN][kTrP];
+#define TR(k) do { if (tr != nullptr && t >= kTr0 && t < kTr0 + kTrN) tr[(t - kTr0) * kTrP + (k)] = clock64(); } while (0)
+#else
+#define TR(k) do { } while (0)
+#endif
+
+__device__ __forceinline__ void bar_cells() { asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory"); }
+
+__device__ __forceinline__ int ld_acquire(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__global__ void __launch_bounds__(THREADS, 1)
+lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(16) float hF[2][SQ][FS];              // [step parity][sequence][unit]
+  __shared__ __align__(8) uint64_t bar_xfull[NXB], bar_xempty[NXB], bar_gates, bar_h;
+  __shared__ uint32_t tmem_slot;
+
+  const int tid = threadIdx.x;
+  const int w = tid >> 5, lane = tid & 31;
+  const int layer = blockIdx.x & 1, grp = blockIdx.x >> 1;
+  const int seq0 = grp * SQ;
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  const int T = a.nsteps;
+  const int nblk = (T + BLK - 1) / BLK;
+  const float* xin = layer ? a.hmid : a.x;
+  float* out = layer ? a.hout : a.hmid;
+  void* planes = layer ? a.hplanes : nullptr;
+
+  if (tid == 0) {
+    for (int i = 0; i < NXB; ++i) {
+      mbar_init(smem_u32(&bar_xfull[i]), N_HELP * 32);
+      mbar_init(smem_u32(&bar_xempty[i]), 1);
+    }
+    mbar_init(smem_u32(&bar_gates), 1);
+    mbar_init(smem_u32(&bar_h), NWARP);
+    fence_mbar_init();
+  }
+  if (w == MMA_WARP) {
+    tmem_alloc(smem_u32(&tmem_slot), 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  // ---------------- prologue: weights -> TMEM (helpers), h_{-1} -> B operand (cell warps) ----------------
+  // cell of this lane (cell warps): unit 4w + gr/2 of sequence 2tq + (gr&1) of each n8 half
+  const int gr = lane >> 2, tq = lane & 3;
+  const bool odd = gr & 1;
+  const int unit = 4 * w + (gr >> 1);
+  const int sl = 2 * tq + (odd ? 1 : 0);
+  float c[2] = {0.f, 0.f};
+  bool valid[2] = {false, false};
+  uint32_t hoffs[2] = {0, 0};    // byte offset of this lane's h element in a plane of the B operand
+  if (w < NWARP) {
+    const float* h0p = a.h0[layer];
+    const float* c0p = a.c0[layer];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int s = j * TS + sl, gseq = seq0 + s;
+      valid[j] = gseq < a.nseq;
+      hoffs[j] = (uint32_t)(s * 128 + (((unit >> 3) ^ (s & 7)) << 4) + (unit & 7) * 2);
+      float h0 = 0.f;
+      if (valid[j] && h0p != nullptr) {
+        h0 = __ldg(h0p + (long long)gseq * kFeat + unit);
+        c[j] = __ldg(c0p + (long long)gseq * kFeat + unit);
+      }
+      uint16_t hh, hl;
+      split1(h0, hh, hl);
+      *reinterpret_cast<uint16_t*>(smem_gen + OFF_H + hoffs[j]) = hh;
+      *reinterpret_cast<uint16_t*>(smem_gen + OFF_H + H_PLANE + hoffs[j]) = hl;
+    }
+    fence_proxy_async_smem();
+  } else if (w < MMA_WARP) {
+    // TMEM lane l of tile tl holds fragment row i = l % 16 of cell warp ww = tl*8 + ((l/16)%2)*4 + l/32 (so that warp
+    // reads its own rows); 32-bit column cc of matrix m holds k = 2cc, 2cc+1. Source: the mma.sync A-fragment
+    // image of [W_ih' | W_hh] (pack.cu pack_lstm_seq_kernel): [warp][k-tile 0..7][plane][lane][reg].
+    const int l = (w & 3) * 32 + lane;
+    const int i = l & 15;
+    const uint32_t* img = reinterpret_cast<const uint32_t*>(a.wfrag[layer]);
+    const uint32_t tl_addr = tmem_base + ((uint32_t)((w & 3) * 32) << 16);
+#pragma unroll 1
+    for (int q = 0; q < 8; ++q) {                 // (matrix, tile, plane)
+      const int m = q >> 2, tile = (q >> 1) & 1, plane = q & 1;
+      const int ww = (tile << 3) | (((l >> 4) & 1) << 2) | (l >> 5);
+      uint32_t v[32];
+#pragma unroll
+      for (int cc = 0; cc < 32; ++cc) {
+        const int kt = m * 4 + (cc >> 3);
+        const int lf = (i & 7) * 4 + (cc & 3);
+        const int reg = (i >= 8 ? 1 : 0) + (((cc & 7) >= 4) ? 2 : 0);
+        v[cc] = __ldg(img + ((size_t)(ww * 8 + kt) * 2 + plane) * 128 + lf * 4 + reg);
+      }
+      const uint32_t col = (uint32_t)((m ? COL_WHH : COL_WIH) + (tile * 2 + plane) * 32);
+      tmem_st_32x16(tl_addr + col, v);
+      tmem_st_32x16(tl_addr + col + 16, v + 16);
+    }
+    tmem_st_wait();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+
+  if (w < NWARP) {
+    // ================= cell warps =================
+    const float b_lo = __ldg(a.bias[layer] + w * 16 + gr), b_hi = __ldg(a.bias[layer] + w * 16 + gr + 8);
+    float* hNp = a.hN[layer];
+    float* cNp = a.cN[layer];
+    // h writer role of the first 256 threads: (sequence tid/16, 4 floats at 4*(tid%16))
+    const int lseq = (tid >> 4) & (SQ - 1), part = tid & 15;
+    const int lg = seq0 + lseq;
+    const bool lvalid = tid < SQ * 16 && lg < a.nseq;
+    const long long hoff = lvalid ? (long long)(lg / a.n_inner) * a.outer + (long long)(lg % a.n_inner) * a.inner : 0;
+    auto flush = [&](int t) {
+      if (!lvalid || (a.exp & 16)) return;
+      const float4 v = *reinterpret_cast<const float4*>(&hF[t & 1][lseq][part * 4]);
+      if (planes != nullptr) {
+        // A operand of the Linear that follows (kernels.cuh planes: [m-tile][32-column chunk][128 x 64 B]): row =
+        // output row index, columns 4 part .. +3 as bf16 hi and lo
+        const long long m = (hoff + (long long)t * a.step) >> 6;
+        const int r = (int)(m & 127);
+        uint8_t* p = reinterpret_cast<uint8_t*>(planes) + ((m >> 7) * 2 + (part >> 3)) * (2 * kPlaneBlock) +
+                     sw64(r, (part & 7) >> 1) + (part & 1) * 8;
+        uint2 h, l;
+        split2(v.x, v.y, h.x, l.x);
+        split2(v.z, v.w, h.y, l.y);
+        *reinterpret_cast<uint2*>(p) = h;
+        *reinterpret_cast<uint2*>(p + a.hp_lo) = l;
+      } else {
+        *reinterpret_cast<float4*>(out + hoff + (long long)t * a.step + part * 4) = v;
+      }
+    };
+    // pre-activations of fragment j -> cell update, h to the B operand and the staging row
+    auto cell = [&](const float (&g)[4], int j, int t) {
+      const float acc0 = g[0] + b_lo, acc1 = g[1] + b_lo, acc2 = g[2] + b_hi, acc3 = g[3] + b_hi;
+      const float s0 = odd ? acc0 : acc1, s1 = odd ? acc2 : acc3;
+      const float r0 = __shfl_xor_sync(0xffffffffu, s0, 4), r1 = __shfl_xor_sync(0xffffffffu, s1, 4);
+      const float ti = fminf(odd ? r0 : acc0, 40.f), tg = fminf(odd ? r1 : acc2, 40.f);
+      const float tf = fminf(odd ? acc1 : r0, 40.f), to = fminf(odd ? acc3 : r1, 40.f);
+      const float ei = ex2_approx(ti), ef = ex2_approx(tf), eg = ex2_approx(tg), eo = ex2_approx(to);
+      const float pi = 1.f + ei, pf = 1.f + ef, pg = 1.f + eg;
+      const float pig = pi * pg;
+      const float cn = fmaf(c[j], pig, (1.f - eg) * pf) * rcp_approx(pf * pig);
+      c[j] = cn;
+      const float ec = ex2_approx(fminf(cn * -2.885390081777927f, 40.f));
+      const float h = (1.f - ec) * rcp_approx((1.f + eo) * (1.f + ec));
+      uint16_t hh, hl;
+      split1(h, hh, hl);
+      *reinterpret_cast<uint16_t*>(smem_gen + OFF_H + hoffs[j]) = hh;
+      *reinterpret_cast<uint16_t*>(smem_gen + OFF_H + H_PLANE + hoffs[j]) = hl;
+      hF[t & 1][j * TS + sl][unit] = h;
+      if (t == T - 1 && valid[j] && hNp != nullptr) {
+        const int gseq = seq0 + j * TS + sl;
+        hNp[(long long)gseq * kFeat + unit] = h;
+        cNp[(long long)gseq * kFeat + unit] = cn;
+      }
+    };
+    // this warp's 16 gate rows: its own TMEM lanes, tile w / 8; columns of step t: buffer, step in block, sequence
+    const uint32_t tw = tmem_base + ((uint32_t)(32 * (w & 3) + 16 * ((w >> 2) & 1)) << 16) + (uint32_t)(COL_ACC + (w >> 3) * (BLK * SQ));
+#ifdef BSB_SEQ2_TRACE
+    long long* tr = (blockIdx.x < 2 && w == 0 && lane == 0) ? &g_seq2_trace[blockIdx.x][0][0][0] : nullptr;
+#endif
+    for (int t = 0; t < T; ++t) {
+      TR(0);
+      mbar_wait(smem_u32(&bar_gates), (uint32_t)(t & 1));
+      tc_fence_after();
+      TR(1);
+      const uint32_t col = (uint32_t)(((t / BLK) & 1) * (2 * BLK * SQ) + (t % BLK) * SQ);
+      float ga[4], gb[4];
+      tmem_ld_frag(tw + col, ga);
+      tmem_ld_frag(tw + col + TS, gb);
+      // bar_gates(t) implies every warp arrived for h_{t-1}: its staging row is complete
+      if (t > 0) flush(t - 1);
+      // ... and before that arrive every warp had flushed step t-2: rows of steps < t-1 are on their way to L2
+      if (layer == 0 && tid == 0 && t > 1 && ((t - 1) % BLK) == 0) {
+        __threadfence();
+        *reinterpret_cast<volatile int*>(a.flags + grp) = t - 1;
+      }
+      tmem_ld_wait_frag2(ga, gb);
+      TR(2);
+      if (!(a.exp & 1)) {
+        cell(ga, 0, t);
+        cell(gb, 1, t);
+      }
+      TR(3);
+      fence_proxy_async_smem();      // h_t (generic-proxy stores) -> visible to the tensor core's operand reads
+      tc_fence_before();             // this warp's tcgen05.ld of the step are ordered before the next MMAs
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&bar_h));
+      TR(4);
+    }
+    bar_cells();
+    flush(T - 1);
+    if (layer == 0) {
+      bar_cells();
+      if (tid == 0) {
+        __threadfence();
+        *reinterpret_cast<volatile int*>(a.flags + grp) = T;
+      }
+    }
+  } else if (w < MMA_WARP) {
+    // ================= helpers: x rows -> bf16 hi/lo B operand of the projection =================
+    const int j = (w - HELP_WARP0) * 32 + lane;     // 0..127: (sequence j/16 and j/16 + 8, 4 floats at 4*(j%16))
+    const int lseq = j >> 4, part = j & 15;
+    const float* xptr[2];
+    bool lvalid[2];
+#pragma unroll
+    for (int s2 = 0; s2 < 2; ++s2) {
+      const int lg = seq0 + s2 * TS + lseq;
+      lvalid[s2] = lg < a.nseq;
+      xptr[s2] = xin;
+      if (lvalid[s2]) xptr[s2] += (long long)(lg / a.n_inner) * a.outer + (long long)(lg % a.n_inner) * a.inner + part * 4;
+    }
+    const int* flag = a.flags + grp;
+    for (int b = 0; b < nblk; ++b) {            // 4 steps x 16 sequences x 64 floats -> planes of buffer b % NXB
+      if (b >= NXB) mbar_wait(smem_u32(&bar_xempty[b % NXB]), ((b / NXB) - 1) & 1);   // MMAs of block b - NXB retired
+      uint8_t* x_hi = smem_gen + OFF_X + (b % NXB) * 2 * X_PLANE;
+      uint8_t* x_lo = x_hi + X_PLANE;
+      if (layer == 1 && !(a.exp & 8)) {         // layer 0 must have published the rows of this block
+        const int need = min((b + 1) * BLK, T);
+        if (lane == 0) {
+          while (ld_acquire(flag) < need) __nanosleep(64);
+        }
+        __syncwarp();
+      }
+      float4 v[2][BLK];
+#pragma unroll
+      for (int s2 = 0; s2 < 2; ++s2)
+#pragma unroll
+        for (int i = 0; i < BLK; ++i) {
+          const int step = b * BLK + i;
+          const float4* p = reinterpret_cast<const float4*>(xptr[s2] + (long long)step * a.step);
+          v[s2][i] = (lvalid[s2] && step < T && !(a.exp & 8)) ? (layer == 1 ? __ldcg(p) : __ldg(p)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+      for (int s2 = 0; s2 < 2; ++s2)
+#pragma unroll
+        for (int i = 0; i < BLK; ++i) {
+          const int r = i * SQ + s2 * TS + lseq;              // row = accumulator column = (step in block, sequence)
+          uint2 h, l;
+          split2(v[s2][i].x, v[s2][i].y, h.x, l.x);
+          split2(v[s2][i].z, v[s2][i].w, h.y, l.y);
+          const uint32_t off = (uint32_t)(r * 128 + (((part >> 1) ^ (r & 7)) << 4) + (part & 1) * 8);
+          *reinterpret_cast<uint2*>(x_hi + off) = h;
+          *reinterpret_cast<uint2*>(x_lo + off) = l;
+        }
+      fence_proxy_async_smem();
+      mbar_arrive(smem_u32(&bar_xfull[b % NXB]));
+    }
+  } else {
+    // ================= tcgen05 issuer =================
+    const uint32_t idesc_x = make_idesc_bf16(128, BLK * SQ);
+    const uint32_t idesc_h = make_idesc_bf16(128, SQ);
+    const uint64_t h_hi = make_sw128_desc(smem_base + OFF_H);
+    const uint64_t h_lo = make_sw128_desc(smem_base + OFF_H + H_PLANE);
+    // W_ih'[tile] . x_block^T -> accumulator buffer b % 2 (overwrites: the block two back is consumed)
+    auto project = [&](int b) {
+      mbar_wait(smem_u32(&bar_xfull[b % NXB]), (uint32_t)((b / NXB) & 1));
+      tc_fence_after();
+      if (elect_one()) {
+        const uint64_t x_hi = make_sw128_desc(smem_base + OFF_X + (b % NXB) * 2 * X_PLANE);
+        const uint64_t x_lo = make_sw128_desc(smem_base + OFF_X + (b % NXB) * 2 * X_PLANE + X_PLANE);
+#pragma unroll
+        for (int tile = 0; tile < 2; ++tile) {
+          const uint32_t d = tmem_base + (uint32_t)(COL_ACC + (b & 1) * (2 * BLK * SQ) + tile * (BLK * SQ));
+          const uint32_t wa_hi = tmem_base + (uint32_t)(COL_WIH + (tile * 2 + 0) * 32);
+          const uint32_t wa_lo = tmem_base + (uint32_t)(COL_WIH + (tile * 2 + 1) * 32);
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk) {
+            const uint64_t adv = (uint64_t)(kk * 32 >> 4);       // 16 bf16 = 32 bytes along K
+            mma_bf16_ts(d, wa_hi + kk * 8, x_lo + adv, idesc_x, kk != 0);   // small terms first
+            mma_bf16_ts(d, wa_lo + kk * 8, x_hi + adv, idesc_x, 1);
+            mma_bf16_ts(d, wa_hi + kk * 8, x_hi + adv, idesc_x, 1);
+          }
+        }
+        mma_commit(smem_u32(&bar_xempty[b % NXB]));
+      }
+      __syncwarp();
+    };
+    project(0);
+#ifdef BSB_SEQ2_TRACE
+    long long* tr = (blockIdx.x < 2 && lane == 0) ? &g_seq2_trace[blockIdx.x][1][0][0] : nullptr;
+#endif
+    for (int t = 0; t < T; ++t) {
+      TR(0);
+      if (t > 0) {
+        mbar_wait(smem_u32(&bar_h), (uint32_t)((t - 1) & 1));      // h_{t-1} is in the B operand
+        tc_fence_after();
+      }
+      TR(1);
+      if (elect_one()) {
+        if (!(a.exp & 2)) {
+#pragma unroll
+          for (int tile = 0; tile < 2; ++tile) {
+            const uint32_t d = tmem_base + (uint32_t)(COL_ACC + ((t / BLK) & 1) * (2 * BLK * SQ) + tile * (BLK * SQ) + (t % BLK) * SQ);
+            const uint32_t wa_hi = tmem_base + (uint32_t)(COL_WHH + (tile * 2 + 0) * 32);
+            const uint32_t wa_lo = tmem_base + (uint32_t)(COL_WHH + (tile * 2 + 1) * 32);
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+              const uint64_t adv = (uint64_t)(kk * 32 >> 4);
+              mma_bf16_ts(d, wa_hi + kk * 8, h_lo + adv, idesc_h, 1);
+              mma_bf16_ts(d, wa_lo + kk * 8, h_hi + adv, idesc_h, 1);
+              mma_bf16_ts(d, wa_hi + kk * 8, h_hi + adv, idesc_h, 1);
+            }
+          }
+        }
+        mma_commit(smem_u32(&bar_gates));
+      }
+      __syncwarp();
+      TR(2);
+      // the projection of the next block executes under the cell update of this step
+      if ((t % BLK) == BLK - 1 && t / BLK + 1 < nblk) project(t / BLK + 1);
+      TR(3);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (w == MMA_WARP) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+#ifdef BSB_SEQ2_TRACE
+extern "C" int bsb_debug_seq2_trace(long long* host, int n) {
+  if (n != 2 * 2 * kTrN * kTrP) return 2 * 2 * kTrN * kTrP;
+  return (int)cudaMemcpyFromSymbol(host, g_seq2_trace, sizeof(long long) * n);
+}
+#endif
+
+}  // namespace
+
+cudaError_t launch_lstm_seq2(const LstmSeq2Args& a, cudaStream_t s) {
+  if (a.nseq <= 0 || a.nsteps <= 0) return cudaSuccess;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(lstm_seq2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  const int groups = (a.nseq + SQ - 1) / SQ;
+  static const int exp_mode = std::getenv("BSB_SEQ2_EXP") ? std::atoi(std::getenv("BSB_SEQ2_EXP")) : 0;
+  LstmSeq2Args b = a;
+  b.exp = exp_mode;
+  cudaError_t e = cudaMemsetAsync(a.flags, 0, sizeof(int) * groups, s);
+  if (e != cudaSuccess) return e;
+  lstm_seq2_kernel<<<2 * groups, THREADS, SMEM_BYTES, s>>>(b);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace bsb

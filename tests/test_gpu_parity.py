@@ -242,7 +242,7 @@ def test_kernels_really_launch(dev, model):
     n0 = _lib.lib().bsb_launch_count()
     model.forward(torch.randn(1, 2050, 2, device=dev))
     torch.cuda.synchronize()
-    assert _lib.lib().bsb_launch_count() - n0 >= 30
+    assert _lib.lib().bsb_launch_count() - n0 >= 25      # 2 layout transposes + the forward's kernels
 
 
 def test_tensor_core_linears_match_fp32_kernels(dev, model, oracle_sd):
