@@ -85,7 +85,7 @@ __device__ __forceinline__ int ld_acquire(const int* p) {
 __global__ void __launch_bounds__(THREADS, 1)
 lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(16) float hF[2][SQ][FS];              // [step parity][sequence][unit]
+  __shared__ __align__(16) float hF[3][SQ][FS];              // [step % 3][sequence][unit]
   __shared__ __align__(8) uint64_t bar_xfull[NXB], bar_xempty[NXB], bar_gates, bar_h;
   __shared__ uint32_t tmem_slot;
 
@@ -148,8 +148,8 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
     }
     fence_proxy_async_smem();
   } else if (w < MMA_WARP) {
-    // TMEM lane l of tile tl holds fragment row i = l % 16 of cell warp ww = tl*8 + ((l/16)%2)*4 + l/32 (so that warp
-    // reads its own rows); 32-bit column cc of matrix m holds k = 2cc, 2cc+1. Source: the mma.sync A-fragment
+    // Weights -> TMEM: lane l of tile tl holds fragment row i = l % 16 of cell warp ww = tl*8 + ((l/16)%2)*4 + l/32 (so
+    // that warp reads its own rows); 32-bit column cc of matrix m (0 = W_ih', 1 = W_hh) holds k = 2cc, 2cc+1. Source: the mma.sync A-fragment
     // image of [W_ih' | W_hh] (pack.cu pack_lstm_seq_kernel): [warp][k-tile 0..7][plane][lane][reg].
     const int l = (w & 3) * 32 + lane;
     const int i = l & 15;
@@ -189,7 +189,7 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
     const long long hoff = lvalid ? (long long)(lg / a.n_inner) * a.outer + (long long)(lg % a.n_inner) * a.inner : 0;
     auto flush = [&](int t) {
       if (!lvalid || (a.exp & 16)) return;
-      const float4 v = *reinterpret_cast<const float4*>(&hF[t & 1][lseq][part * 4]);
+      const float4 v = *reinterpret_cast<const float4*>(&hF[t % 3][lseq][part * 4]);
       if (planes != nullptr) {
         // A operand of the Linear that follows (kernels.cuh planes: [m-tile][32-column chunk][128 x 64 B]): row =
         // output row index, columns 4 part .. +3 as bf16 hi and lo
@@ -224,7 +224,7 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
       split1(h, hh, hl);
       *reinterpret_cast<uint16_t*>(smem_gen + OFF_H + hoffs[j]) = hh;
       *reinterpret_cast<uint16_t*>(smem_gen + OFF_H + H_PLANE + hoffs[j]) = hl;
-      hF[t & 1][j * TS + sl][unit] = h;
+      hF[t % 3][j * TS + sl][unit] = h;
       if (t == T - 1 && valid[j] && hNp != nullptr) {
         const int gseq = seq0 + j * TS + sl;
         hNp[(long long)gseq * kFeat + unit] = h;
@@ -245,13 +245,6 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
       float ga[4], gb[4];
       tmem_ld_frag(tw + col, ga);
       tmem_ld_frag(tw + col + TS, gb);
-      // bar_gates(t) implies every warp arrived for h_{t-1}: its staging row is complete
-      if (t > 0) flush(t - 1);
-      // ... and before that arrive every warp had flushed step t-2: rows of steps < t-1 are on their way to L2
-      if (layer == 0 && tid == 0 && t > 1 && ((t - 1) % BLK) == 0) {
-        __threadfence();
-        *reinterpret_cast<volatile int*>(a.flags + grp) = t - 1;
-      }
       tmem_ld_wait_frag2(ga, gb);
       TR(2);
       if (!(a.exp & 1)) {
@@ -264,6 +257,16 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&bar_h));
       TR(4);
+      // rows of step t-1 go out while the tensor core works on step t+1 (complete since bar_gates(t); the staging
+      // buffer is reused by step t+2, which nobody reaches before this warp's next arrive)
+      if (t > 0) flush(t - 1);
+      TR(5);
+      // bar_gates(t) implied every warp's arrive for h_{t-1}, and before that arrive every warp had flushed step
+      // t-3: rows of steps < t-2 are on their way to L2. Published by a thread with no rows to flush.
+      if (layer == 0 && tid == NT - 32 && t > 2 && ((t - 2) % BLK) == 0) {
+        __threadfence();
+        *reinterpret_cast<volatile int*>(a.flags + grp) = t - 2;
+      }
     }
     bar_cells();
     flush(T - 1);
@@ -329,7 +332,9 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
     const uint32_t idesc_h = make_idesc_bf16(128, SQ);
     const uint64_t h_hi = make_sw128_desc(smem_base + OFF_H);
     const uint64_t h_lo = make_sw128_desc(smem_base + OFF_H + H_PLANE);
-    // W_ih'[tile] . x_block^T -> accumulator buffer b % 2 (overwrites: the block two back is consumed)
+    // W_ih'[tile] . x_block^T -> accumulator buffer b % 2 (overwrites: the block two back is consumed). ~1,200 cycles
+    // of tensor time per block (measured: ~50 per N = 64 MMA in TS form, ~70 in SS form with the weights in shared
+    // memory; issuing it in four parts, one per step, cost more than it hid).
     auto project = [&](int b) {
       mbar_wait(smem_u32(&bar_xfull[b % NXB]), (uint32_t)((b / NXB) & 1));
       tc_fence_after();
@@ -398,14 +403,14 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
   }
 }
 
+}  // namespace
+
 #ifdef BSB_SEQ2_TRACE
 extern "C" int bsb_debug_seq2_trace(long long* host, int n) {
   if (n != 2 * 2 * kTrN * kTrP) return 2 * 2 * kTrN * kTrP;
   return (int)cudaMemcpyFromSymbol(host, g_seq2_trace, sizeof(long long) * n);
 }
 #endif
-
-}  // namespace
 
 cudaError_t launch_lstm_seq2(const LstmSeq2Args& a, cudaStream_t s) {
   if (a.nseq <= 0 || a.nsteps <= 0) return cudaSuccess;

@@ -18,12 +18,12 @@ buf = (ctypes.c_longlong * n)()
 l.bsb_debug_seq2_trace.argtypes = [ctypes.c_void_p, ctypes.c_int]
 assert l.bsb_debug_seq2_trace(buf, n) == 0
 v = torch.tensor(list(buf)).reshape(2, 2, 8, 8)
-cell_names = ["wait gates", "ld+flush+wait", "cell", "fence+arrive"]
+cell_names = ["wait gates", "ld+wait", "cell", "fence+arrive", "flush"]
 mma_names = ["wait h", "issue+commit", "projection"]
 for cta in range(2):
     for role in range(2):
         d = v[cta, role]
-        k = 5 if role == 0 else 4
+        k = 6 if role == 0 else 4
         seg = (d[:, 1:k] - d[:, :k - 1]).double().mean(0)
         step = (d[1:, 0] - d[:-1, 0]).double().mean()
         nm = cell_names if role == 0 else mma_names
