@@ -383,10 +383,9 @@ int run_rnn_block(int j, const float* fin, int C, int T, const void* packed, con
     return 0;
   }
   if (!band && T >= kLstmSeqMinSteps && !force_ffma()) {
-    // latency path: 8 sequences per CTA, fc_in and W_ih fused into the recurrence (lstm_seq.cu)
+    // latency path: both layers in one launch, fc_in and W_ih fused into the recurrence (lstm_seq2.cu)
     float* hl[2] = {w.hbuf, w.xproj};
-    static const bool one_layer_launches = std::getenv("BSB_SEQ1") != nullptr;     // A/B switch: lstm_seq.cu
-    if (!one_layer_launches) {
+    {
       LstmSeq2Args a{};
       a.x = fin; a.hmid = hl[0]; a.hout = hl[1];
       a.nseq = C * kBands; a.nsteps = T; a.n_inner = kBands;
@@ -402,25 +401,6 @@ int run_rnn_block(int j, const float* fin, int C, int T, const void* packed, con
       a.flags = reinterpret_cast<int*>(w.t64);                // t64 is only used by the FFMA fallback path
       CK(launch_lstm_seq2(a, s));
       std::snprintf(nm, sizeof(nm), "rnn%d.rec", j);
-      mark(nm, s);
-    }
-    for (int layer = 0; one_layer_launches && layer < 2; ++layer) {
-      LstmSeqArgs a{};
-      a.x = layer == 0 ? fin : hl[0];
-      a.hout = hl[layer];
-      a.wfrag = PW(packed, R.sqw[layer]);
-      a.bias = PW(packed, R.sqb[layer]);
-      a.nseq = C * kBands; a.nsteps = T; a.n_inner = kBands;
-      a.x_outer = a.h_outer = (long long)T * kBands * kFeat;
-      a.x_inner = a.h_inner = kFeat;
-      a.x_step = a.h_step = (long long)kBands * kFeat;
-      const long long per = (long long)a.nseq * kFeat;       // state [2(h,c)][2 layers][nseq][64]
-      if (st_in) { a.h0 = st_in + layer * per; a.c0 = st_in + (2 + layer) * per; }
-      if (st_out) { a.hN = st_out + layer * per; a.cN = st_out + (2 + layer) * per; }
-      const bool planes = layer == 1 && rows >= kTcMinRows;           // the fc below runs on the tensor-core kernel
-      if (planes) { a.hplanes = w.planeA; a.hp_lo = kPlaneBlock; }
-      CK(launch_lstm_seq(a, s));
-      std::snprintf(nm, sizeof(nm), "rnn%d.rec%d", j, layer);
       mark(nm, s);
     }
     if (rows >= kTcMinRows)

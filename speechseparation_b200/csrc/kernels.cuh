@@ -100,25 +100,6 @@ struct LstmTcArgs {
   long long hp_lo;
 };
 cudaError_t launch_lstm_tc(const LstmTcArgs& a, cudaStream_t s);
-// Time-axis LSTM layer with the input projection fused, 8 sequences per CTA on mma.sync (lstm_seq.cu).
-// Sequence addressing as LstmArgs: (seq / n_inner) * outer + (seq % n_inner) * inner + step * step.
-struct LstmSeqArgs {
-  const float* x;            // 64 input features per (seq, step)
-  float* hout;               // 64 outputs per (seq, step)
-  const void* wfrag;         // layout.h RnnBlock::sqw
-  const float* bias;         // RnnBlock::sqb
-  const float* h0;           // optional initial state [nseq][64]
-  const float* c0;
-  float* hN;                 // optional final state
-  float* cN;
-  long long x_outer, x_inner, x_step, h_outer, h_inner, h_step;
-  int n_inner, nseq, nsteps;
-  // optional: h goes out as bf16 hi/lo planes (LinProb::Ap geometry, one 64-column chunk, row = h offset / 64)
-  // for the Linear that follows, instead of fp32 rows at hout
-  void* hplanes;
-  long long hp_lo;
-};
-cudaError_t launch_lstm_seq(const LstmSeqArgs& a, cudaStream_t s);
 // Both layers of a time-axis block in ONE launch, 16 sequences per group, layer 1 a few steps behind layer 0
 // (lstm_seq2.cu). x, hmid (layer-0 output = layer-1 input) and hout share one addressing:
 // (seq / n_inner) * outer + (seq % n_inner) * inner + step * step.
@@ -137,7 +118,8 @@ struct LstmSeq2Args {
   void* hplanes;             // optional: layer-1 h as bf16 hi/lo planes instead of fp32 rows at hout
   long long hp_lo;
   int* flags;                // [ceil(nseq / 16)] ints of scratch (zeroed by the launch)
-  int exp;                   // experiment switches (BSB_SEQ2_EXP), 0 in production
+  int exp;                   // timing-experiment switches (BSB_SEQ2_EXP: 1 no cell update, 2 no recurrent MMAs, 8 no x loads,
+                             // 16 no h flush), 0 in production
 };
 cudaError_t launch_lstm_seq2(const LstmSeq2Args& a, cudaStream_t s);
 constexpr int kLstmSeqMinSteps = 2;  // single steps (streaming hops) stay on the FFMA recurrence

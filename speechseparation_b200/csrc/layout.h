@@ -56,13 +56,12 @@ struct RnnBlock {
   long long tcw[2][2];
   long long tcb[2][2];
   // time-axis blocks (ndir == 1) only: per layer, the same matrix as mma.sync A fragments
-  // [warp 16][k-tile 8][plane 2][lane 32][4 words] and the bias [warp 16][16 rows] (lstm_seq.cu)
+  // [warp 16][k-tile 8][plane 2][lane 32][4 words] and the bias [warp 16][16 rows] (lstm_seq2.cu gathers its TMEM weight image from it)
   long long sqw[2];
   long long sqb[2];
 };
 constexpr long long kSeqFragFloats = 16 * 8 * 2 * 32 * 4;         // mma.sync A fragments of [W_ih' | W_hh]
-constexpr long long kSeqXImgFloats = 2 * kGates * 64 * 2 / 4;      // W_ih' again as tcgen05 B operand: bf16 hi/lo [256][64], SWIZZLE_128B
-constexpr long long kSeqImgFloats = kSeqFragFloats + kSeqXImgFloats;
+constexpr long long kSeqImgFloats = kSeqFragFloats;
 inline constexpr int tc_lstm_kin(int layer, int ndir) { return layer == 0 ? kFeat : kFeat * ndir; }
 inline constexpr int tc_lstm_chunks(int layer, int ndir) { return (tc_lstm_kin(layer, ndir) + kFeat) / 64; }
 inline constexpr long long tc_lstm_img_floats(int layer, int ndir) {   // 2 planes x chunks x 256 x 64 bf16

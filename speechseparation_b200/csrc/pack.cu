@@ -96,7 +96,7 @@ __global__ void pack_lstm_tc_kernel(const float* __restrict__ w_ih, const float*
   if (k == 0) bias[n] = lstm_cat_bias(row, w_ih, b_ih, b_hh, w_in, b_in);
 }
 
-// mma.sync fragment image of the same matrix for the time-axis kernel (lstm_seq.cu, kin = 64):
+// mma.sync fragment image of the same matrix for the time-axis kernel (lstm_seq2.cu, kin = 64):
 // block (warp w, k-tile kt, plane p), thread (lane, reg): the m16n8k16 A fragment word `reg` of `lane`
 // for the 16 gate rows of warp w (rows 0-7: i,f of units 4w..4w+3 interleaved; rows 8-15: g,o).
 __device__ __forceinline__ int seq_row_of(int w, int rm) {
@@ -125,20 +125,6 @@ __global__ void pack_lstm_seq_kernel(const float* __restrict__ w_ih, const float
     bias[w * 16 + threadIdx.x] = lstm_cat_bias(seq_row_of(w, threadIdx.x), w_ih, b_ih, b_hh, w_in, b_in);
 }
 
-// The input half W_ih' of the same matrix once more, as the tcgen05 B operand of the time-axis kernel:
-// column c = 16 w + rm of the accumulator is gate row seq_row_of(w, rm); [256 rows][64 k] bf16, 128B-swizzled
-// K-major, hi plane then lo plane.
-__global__ void pack_lstm_seq_x_kernel(const float* __restrict__ w_ih, const float* __restrict__ w_hh,
-                                       const float* __restrict__ w_in, uint8_t* __restrict__ img) {
-  const int c = blockIdx.x, k = threadIdx.x;
-  const float wf = lstm_cat_weight(seq_row_of(c >> 4, c & 15), k, kFeat, w_ih, w_hh, w_in);
-  const __nv_bfloat16 h = __float2bfloat16_rn(wf);
-  const __nv_bfloat16 l = __float2bfloat16_rn(wf - __bfloat162float(h));
-  const size_t off = (size_t)c * 128 + ((((k >> 3) ^ (c & 7))) << 4) + (k & 7) * 2;
-  *reinterpret_cast<__nv_bfloat16*>(img + off) = h;
-  *reinterpret_cast<__nv_bfloat16*>(img + (size_t)kGates * 128 + off) = l;
-}
-
 }  // namespace
 
 cudaError_t launch_pack_lstm_tc(const float* w_ih, const float* w_hh, const float* b_ih, const float* b_hh,
@@ -154,8 +140,7 @@ cudaError_t launch_pack_lstm_seq(const float* w_ih, const float* w_hh, const flo
                                  const float* w_in, const float* b_in, void* img, float* bias, cudaStream_t s) {
   pack_lstm_seq_kernel<<<dim3(16, 8, 2), 128, 0, s>>>(w_ih, w_hh, b_ih, b_hh, w_in, b_in,
                                                       reinterpret_cast<uint32_t*>(img), bias);
-  pack_lstm_seq_x_kernel<<<kGates, kFeat, 0, s>>>(w_ih, w_hh, w_in, reinterpret_cast<uint8_t*>(img) + kSeqFragFloats * 4);
-  count_launch(2);
+  count_launch();
   return cudaGetLastError();
 }
 
