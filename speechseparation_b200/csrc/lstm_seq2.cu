@@ -42,7 +42,8 @@ constexpr int TS = 8;            // sequences per accumulator fragment
 constexpr int NWARP = 16;        // cell warps
 constexpr int NT = NWARP * 32;
 constexpr int HELP_WARP0 = NWARP, N_HELP = 4, MMA_WARP = NWARP + N_HELP;
-constexpr int THREADS = (MMA_WARP + 1) * 32;
+constexpr int N_MMA = 2;         // issuer warps: one per M = 128 gate-row tile
+constexpr int THREADS = (MMA_WARP + N_MMA) * 32;
 constexpr int FS = 68;           // fp32 row stride of the h staging buffers
 constexpr int BLK = 4;           // steps per projection block (4 steps x 16 sequences = 64 columns per tile)
 constexpr int NXB = 4;           // x-block buffers in shared memory
@@ -86,7 +87,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(16) float hF[3][SQ][FS];              // [step % 3][sequence][unit]
-  __shared__ __align__(8) uint64_t bar_xfull[NXB], bar_xempty[NXB], bar_gates, bar_h;
+  __shared__ __align__(8) uint64_t bar_xfull[NXB], bar_xempty[NXB], bar_gates[2], bar_h;
   __shared__ uint32_t tmem_slot;
 
   const int tid = threadIdx.x;
@@ -104,9 +105,10 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
   if (tid == 0) {
     for (int i = 0; i < NXB; ++i) {
       mbar_init(smem_u32(&bar_xfull[i]), N_HELP * 32);
-      mbar_init(smem_u32(&bar_xempty[i]), 1);
+      mbar_init(smem_u32(&bar_xempty[i]), N_MMA);
     }
-    mbar_init(smem_u32(&bar_gates), 1);
+    mbar_init(smem_u32(&bar_gates[0]), 1);
+    mbar_init(smem_u32(&bar_gates[1]), 1);
     mbar_init(smem_u32(&bar_h), NWARP);
     fence_mbar_init();
   }
@@ -238,7 +240,7 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
 #endif
     for (int t = 0; t < T; ++t) {
       TR(0);
-      mbar_wait(smem_u32(&bar_gates), (uint32_t)(t & 1));
+      mbar_wait(smem_u32(&bar_gates[w >> 3]), (uint32_t)(t & 1));    // (polling with test_wait measured slower)
       tc_fence_after();
       TR(1);
       const uint32_t col = (uint32_t)(((t / BLK) & 1) * (2 * BLK * SQ) + (t % BLK) * SQ);
@@ -327,32 +329,32 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
       mbar_arrive(smem_u32(&bar_xfull[b % NXB]));
     }
   } else {
-    // ================= tcgen05 issuer =================
+    // ================= tcgen05 issuers: warp MMA_WARP + tile owns the M = 128 gate-row tile `tile` =================
+    // (the MMAs of the two tiles touch disjoint accumulator columns; two issuing threads halve the issue time
+    // of a step, and the cell warps of a tile start as soon as their own 12 MMAs have retired)
+    const int tile = w - MMA_WARP;
     const uint32_t idesc_x = make_idesc_bf16(128, BLK * SQ);
     const uint32_t idesc_h = make_idesc_bf16(128, SQ);
     const uint64_t h_hi = make_sw128_desc(smem_base + OFF_H);
     const uint64_t h_lo = make_sw128_desc(smem_base + OFF_H + H_PLANE);
-    // W_ih'[tile] . x_block^T -> accumulator buffer b % 2 (overwrites: the block two back is consumed). ~1,200 cycles
-    // of tensor time per block (measured: ~50 per N = 64 MMA in TS form, ~70 in SS form with the weights in shared
-    // memory; issuing it in four parts, one per step, cost more than it hid).
+    const uint32_t wih_hi = tmem_base + (uint32_t)(COL_WIH + (tile * 2 + 0) * 32), wih_lo = wih_hi + 32;
+    const uint32_t whh_hi = tmem_base + (uint32_t)(COL_WHH + (tile * 2 + 0) * 32), whh_lo = whh_hi + 32;
+    // W_ih'[tile] . x_block^T -> accumulator buffer b % 2 (overwrites: the block two back is consumed). ~50 cycles per
+    // N = 64 MMA in TS form (~70 in SS form with the weights in shared memory; issuing it in four parts, one per
+    // step, cost more than it hid).
     auto project = [&](int b) {
       mbar_wait(smem_u32(&bar_xfull[b % NXB]), (uint32_t)((b / NXB) & 1));
       tc_fence_after();
       if (elect_one()) {
         const uint64_t x_hi = make_sw128_desc(smem_base + OFF_X + (b % NXB) * 2 * X_PLANE);
         const uint64_t x_lo = make_sw128_desc(smem_base + OFF_X + (b % NXB) * 2 * X_PLANE + X_PLANE);
+        const uint32_t d = tmem_base + (uint32_t)(COL_ACC + (b & 1) * (2 * BLK * SQ) + tile * (BLK * SQ));
 #pragma unroll
-        for (int tile = 0; tile < 2; ++tile) {
-          const uint32_t d = tmem_base + (uint32_t)(COL_ACC + (b & 1) * (2 * BLK * SQ) + tile * (BLK * SQ));
-          const uint32_t wa_hi = tmem_base + (uint32_t)(COL_WIH + (tile * 2 + 0) * 32);
-          const uint32_t wa_lo = tmem_base + (uint32_t)(COL_WIH + (tile * 2 + 1) * 32);
-#pragma unroll
-          for (int kk = 0; kk < 4; ++kk) {
-            const uint64_t adv = (uint64_t)(kk * 32 >> 4);       // 16 bf16 = 32 bytes along K
-            mma_bf16_ts(d, wa_hi + kk * 8, x_lo + adv, idesc_x, kk != 0);   // small terms first
-            mma_bf16_ts(d, wa_lo + kk * 8, x_hi + adv, idesc_x, 1);
-            mma_bf16_ts(d, wa_hi + kk * 8, x_hi + adv, idesc_x, 1);
-          }
+        for (int kk = 0; kk < 4; ++kk) {
+          const uint64_t adv = (uint64_t)(kk * 32 >> 4);       // 16 bf16 = 32 bytes along K
+          mma_bf16_ts(d, wih_hi + kk * 8, x_lo + adv, idesc_x, kk != 0);   // small terms first
+          mma_bf16_ts(d, wih_lo + kk * 8, x_hi + adv, idesc_x, 1);
+          mma_bf16_ts(d, wih_hi + kk * 8, x_hi + adv, idesc_x, 1);
         }
         mma_commit(smem_u32(&bar_xempty[b % NXB]));
       }
@@ -360,7 +362,7 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
     };
     project(0);
 #ifdef BSB_SEQ2_TRACE
-    long long* tr = (blockIdx.x < 2 && lane == 0) ? &g_seq2_trace[blockIdx.x][1][0][0] : nullptr;
+    long long* tr = (blockIdx.x < 2 && tile == 0 && lane == 0) ? &g_seq2_trace[blockIdx.x][1][0][0] : nullptr;
 #endif
     for (int t = 0; t < T; ++t) {
       TR(0);
@@ -371,21 +373,16 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
       TR(1);
       if (elect_one()) {
         if (!(a.exp & 2)) {
+          const uint32_t d = tmem_base + (uint32_t)(COL_ACC + ((t / BLK) & 1) * (2 * BLK * SQ) + tile * (BLK * SQ) + (t % BLK) * SQ);
 #pragma unroll
-          for (int tile = 0; tile < 2; ++tile) {
-            const uint32_t d = tmem_base + (uint32_t)(COL_ACC + ((t / BLK) & 1) * (2 * BLK * SQ) + tile * (BLK * SQ) + (t % BLK) * SQ);
-            const uint32_t wa_hi = tmem_base + (uint32_t)(COL_WHH + (tile * 2 + 0) * 32);
-            const uint32_t wa_lo = tmem_base + (uint32_t)(COL_WHH + (tile * 2 + 1) * 32);
-#pragma unroll
-            for (int kk = 0; kk < 4; ++kk) {
-              const uint64_t adv = (uint64_t)(kk * 32 >> 4);
-              mma_bf16_ts(d, wa_hi + kk * 8, h_lo + adv, idesc_h, 1);
-              mma_bf16_ts(d, wa_lo + kk * 8, h_hi + adv, idesc_h, 1);
-              mma_bf16_ts(d, wa_hi + kk * 8, h_hi + adv, idesc_h, 1);
-            }
+          for (int kk = 0; kk < 4; ++kk) {
+            const uint64_t adv = (uint64_t)(kk * 32 >> 4);
+            mma_bf16_ts(d, whh_hi + kk * 8, h_lo + adv, idesc_h, 1);
+            mma_bf16_ts(d, whh_lo + kk * 8, h_hi + adv, idesc_h, 1);
+            mma_bf16_ts(d, whh_hi + kk * 8, h_hi + adv, idesc_h, 1);
           }
         }
-        mma_commit(smem_u32(&bar_gates));
+        mma_commit(smem_u32(&bar_gates[tile]));
       }
       __syncwarp();
       TR(2);
