@@ -462,3 +462,19 @@ def test_train_infer_metrics_vs_oracle(dev, model, oracle_sd):
         assert abs(a - b) < 0.01, (got, want)            # dB
     with pytest.raises(RuntimeError):
         train_infer(model, (wav, src))                   # host tensors: no CPU path
+
+
+def test_many_session_streaming_cfg4_shape(dev, model, oracle_sd):
+    """cfg 4 (hop-synchronous serving of many sessions): 65 sessions x 2 rows = 130 rows per hop, enough rows for
+    the tensor-core Linear / band-LSTM kernels inside forward_recurrent; carried state, graph replay from hop 2."""
+    from speechseparation_b200 import StreamingSeparator
+    rows, hops = 130, 4
+    wav, _ = O.synth_audio(rows, hops * 1024, seed=31)
+    ref, ref_state = O.stream(oracle_sd, wav)
+    sep = StreamingSeparator(model, rows=rows)
+    outs = [sep.step(wav[:, h * 1024:(h + 1) * 1024].to(dev)).clone() for h in range(hops)]
+    got = torch.cat(outs, 1).cpu()
+    for r in range(0, rows, 13):
+        assert rel(got[r], ref[r]) < STAGE_TOL, r
+    assert rel(got, ref) < STAGE_TOL
+    assert float((sep.current_state.cpu() - ref_state).abs().max()) < 1e-4
