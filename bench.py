@@ -421,6 +421,16 @@ def main():
     }
     if world == 1 and not args.no_streaming:
         res["streaming"] = streaming_latency(model, dev, hops=args.stream_hops)
+        # BASELINE.json configs[3]: 512 concurrent sessions (1,024 rows) advanced hop-synchronously; on G GPUs every
+        # GPU holds 1024/G rows (sessions are independent, shard.py), so the per-GPU shapes are these row counts
+        sess = {}
+        for g_, rows_ in ((1, 1024), (2, 512), (4, 256), (8, 128)):
+            r = streaming_latency(model, dev, hops=100, rows=rows_)
+            sess[f"{rows_}_rows"] = {"as_on_gpus": g_, "device_ms_p50": r["device_ms_p50"], "device_ms_p99": r["device_ms_p99"],
+                                     "host_ms_p99": r["host_ms_p99"],
+                                     "sessions_per_gpu_realtime": (rows_ // 2) * r["hop_budget_ms"] / r["host_ms_p99"]}
+        res["streaming_sessions"] = {"config": "cfg 4: 512 sessions x 2 rows, hop-synchronous batched step, per-GPU row counts "
+                                               "for 1/2/4/8 GPUs measured on one GPU", **sess}
     if world == 1 and not args.no_cpu_baseline:
         res["cpu_baseline"] = cpu_baseline(min(rows, 4), n)
     print(json.dumps(res))

@@ -478,3 +478,14 @@ def test_many_session_streaming_cfg4_shape(dev, model, oracle_sd):
         assert rel(got[r], ref[r]) < STAGE_TOL, r
     assert rel(got, ref) < STAGE_TOL
     assert float((sep.current_state.cpu() - ref_state).abs().max()) < 1e-4
+
+
+def test_long_form_cfg5_shape(dev, model, oracle_sd):
+    """cfg 5 shape (one long clip per GPU): 1 row x 60 s = 2,584 frames; 12 time-axis sequences -> ONE sequence
+    group walks 2,584 steps (646 projection blocks, flag publications and buffer cycles), the band-axis kernels see
+    2,584 x 12-step sequences. Waveform gate against the oracle."""
+    wav, _ = O.synth_audio(1, 60 * 44100, seed=41)
+    ref = O.separate(oracle_sd, wav)
+    out = model.separate(wav.to(dev))
+    assert out.shape == ref.shape == (1, 1024 * 2583)
+    assert O.max_rel_err(out.cpu(), ref) < GATE / 5
