@@ -117,7 +117,8 @@ struct LstmSeq2Args {
   int n_inner, nseq, nsteps;
   void* hplanes;             // optional: layer-1 h as bf16 hi/lo planes instead of fp32 rows at hout
   long long hp_lo;
-  int* flags;                // [ceil(nseq / 16)] ints of scratch (zeroed by the launch)
+  int* flags;                // [ceil(nseq / 8)] ints of scratch (zeroed by the launch)
+  int group;                 // sequences per CTA (8 or 16), chosen by the launch
   int exp;                   // timing-experiment switches (BSB_SEQ2_EXP: 1 no cell update, 2 no recurrent MMAs, 8 no x loads,
                              // 16 no h flush), 0 in production
 };

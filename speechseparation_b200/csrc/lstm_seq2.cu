@@ -93,7 +93,8 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
   const int tid = threadIdx.x;
   const int w = tid >> 5, lane = tid & 31;
   const int layer = blockIdx.x & 1, grp = blockIdx.x >> 1;
-  const int seq0 = grp * SQ;
+  const int sq = a.group;          // sequences this CTA really owns: 16, or 8 (only fragment 0) when that still fits the SMs
+  const int seq0 = grp * sq;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
   const int T = a.nsteps;
@@ -136,7 +137,7 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
       const int s = j * TS + sl, gseq = seq0 + s;
-      valid[j] = gseq < a.nseq;
+      valid[j] = s < sq && gseq < a.nseq;
       hoffs[j] = (uint32_t)(s * 128 + (((unit >> 3) ^ (s & 7)) << 4) + (unit & 7) * 2);
       float h0 = 0.f;
       if (valid[j] && h0p != nullptr) {
@@ -187,7 +188,7 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
     // h writer role of the first 256 threads: (sequence tid/16, 4 floats at 4*(tid%16))
     const int lseq = (tid >> 4) & (SQ - 1), part = tid & 15;
     const int lg = seq0 + lseq;
-    const bool lvalid = tid < SQ * 16 && lg < a.nseq;
+    const bool lvalid = tid < sq * 16 && lg < a.nseq;
     const long long hoff = lvalid ? (long long)(lg / a.n_inner) * a.outer + (long long)(lg % a.n_inner) * a.inner : 0;
     auto flush = [&](int t) {
       if (!lvalid || (a.exp & 16)) return;
@@ -251,7 +252,7 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
       TR(2);
       if (!(a.exp & 1)) {
         cell(ga, 0, t);
-        cell(gb, 1, t);
+        if (sq > TS) cell(gb, 1, t);     // (h of the unused half stays zero in the B operand)
       }
       TR(3);
       fence_proxy_async_smem();      // h_t (generic-proxy stores) -> visible to the tensor core's operand reads
@@ -288,7 +289,7 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
 #pragma unroll
     for (int s2 = 0; s2 < 2; ++s2) {
       const int lg = seq0 + s2 * TS + lseq;
-      lvalid[s2] = lg < a.nseq;
+      lvalid[s2] = s2 * TS < sq && lg < a.nseq;
       xptr[s2] = xin;
       if (lvalid[s2]) xptr[s2] += (long long)(lg / a.n_inner) * a.outer + (long long)(lg % a.n_inner) * a.inner + part * 4;
     }
@@ -417,10 +418,16 @@ cudaError_t launch_lstm_seq2(const LstmSeq2Args& a, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
-  const int groups = (a.nseq + SQ - 1) / SQ;
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  // 8 sequences per CTA halve the cell update of a step (one fragment per lane instead of two); taken when all
+  // CTAs are still co-resident, i.e. for short batches and long-form clips (cfg 1, 3, 5)
+  const int group = 2 * ((a.nseq + TS - 1) / TS) <= sms ? TS : SQ;
+  const int groups = (a.nseq + group - 1) / group;
   static const int exp_mode = std::getenv("BSB_SEQ2_EXP") ? std::atoi(std::getenv("BSB_SEQ2_EXP")) : 0;
   LstmSeq2Args b = a;
   b.exp = exp_mode;
+  b.group = (exp_mode & 128) ? SQ : group;
   cudaError_t e = cudaMemsetAsync(a.flags, 0, sizeof(int) * groups, s);
   if (e != cudaSuccess) return e;
   lstm_seq2_kernel<<<2 * groups, THREADS, SMEM_BYTES, s>>>(b);

@@ -319,12 +319,13 @@ def test_band_axis_tensor_core_lstm_vs_oracle(dev, model, oracle_sd, C, T):
 
 @pytest.mark.parametrize("C,T,with_state", [(1, 2, False), (1, 3, True), (2, 37, True), (3, 130, False), (5, 64, True),
                                              (1, 15, True), (1, 16, False), (2, 17, True), (1, 33, False), (2, 100, True),
-                                             (1, 4, True), (1, 5, False), (1, 9, True), (4, 8, False), (100, 9, True)])
+                                             (1, 4, True), (1, 5, False), (1, 9, True), (4, 8, False), (100, 9, True), (50, 21, True), (51, 6, False)])
 def test_time_axis_lstm_vs_oracle_with_state(dev, model, oracle_sd, C, T, with_state):
     """TimewiseLSTM blocks (bsrnn.py:101-128) on the two-layer wavefront kernel (lstm_seq2.cu, 16 sequences per
     CTA): ragged last group (12, 24, 36, 60 sequences), a full one (48), more CTAs than SMs (1200 sequences ->
-    150 CTAs), step counts around the 4-step projection blocks / flag publications and the buffer cycles,
-    initial (h, c) in, final (h, c) out, against the ATen LSTM."""
+    150 CTAs), both group sizes (8 sequences per CTA up to 592 sequences, 16 beyond: 600 and 612 sequences have a
+    half-empty last group), step counts around the 4-step projection blocks / flag publications and the buffer
+    cycles, initial (h, c) in, final (h, c) out, against the ATen LSTM."""
     from speechseparation_b200 import _lib
     l = _lib.lib()
     packed = model.packed_weights(dev)
