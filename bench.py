@@ -354,6 +354,10 @@ def main():
     # ---- per-kernel accounting and the roofline of the dominant kernel -------------------------------
     pk = peaks()
     flops, byt = stage_work(T)
+    for j in (1, 3):                       # time-axis block with its output Linear fused into the wavefront launch
+        if f"rnn{j}.fc" not in stage_ms and f"rnn{j}.rec" in stage_ms:
+            flops[f"rnn{j}.rec"] += flops[f"rnn{j}.fc"]
+            byt[f"rnn{j}.rec"] += byt[f"rnn{j}.fc"] - 2 * 12 * 64 * 4      # h of layer 1 no longer leaves and re-enters as planes
     total_ms = sum(stage_ms.values())
     kern = {}
     for st_name, ms in stage_ms.items():

@@ -399,10 +399,12 @@ int run_rnn_block(int j, const float* fin, int C, int T, const void* packed, con
       }
       if (rows >= kTcMinRows) { a.hplanes = w.planeA; a.hp_lo = kPlaneBlock; }
       a.flags = reinterpret_cast<int*>(w.t64);                // t64 is only used by the FFMA fallback path
+      a.fcw = PW(packed, R.fc.w); a.ldfcw = R.fc.Kpad; a.fcb = PW(packed, R.fc.b); a.fc_out = fout;
       CK(launch_lstm_seq2(a, s));
       std::snprintf(nm, sizeof(nm), "rnn%d.rec", j);
       mark(nm, s);
     }
+    if (lstm_seq2_fused_fc()) return 0;                        // the launch carried fc + residual (third CTA per group)
     if (rows >= kTcMinRows)
       CKI(single_linear(packed, R.fc, hl[1], ldh, fout, kFeat, rows, ACT_NONE, fin, kFeat, s, w.planeA, kPlaneBlock));
     else

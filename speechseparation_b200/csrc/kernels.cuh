@@ -117,12 +117,19 @@ struct LstmSeq2Args {
   int n_inner, nseq, nsteps;
   void* hplanes;             // optional: layer-1 h as bf16 hi/lo planes instead of fp32 rows at hout
   long long hp_lo;
-  int* flags;                // [ceil(nseq / 8)] ints of scratch (zeroed by the launch)
+  int* flags;                // [2 * groups] ints of scratch (zeroed by the launch)
   int group;                 // sequences per CTA (8 or 16), chosen by the launch
+  // optional: the block's output Linear + residual fused as a third CTA per group: fc_out = W_fc . h_layer1 + b + x
+  const float* fcw;          // fp32 [64][ldfcw]
+  const float* fcb;          // [64]
+  float* fc_out;             // same addressing as x; must not alias x
+  int ldfcw;
+  int fuse_fc, ngroups;      // set by the launch
   int exp;                   // timing-experiment switches (BSB_SEQ2_EXP: 1 no cell update, 2 no recurrent MMAs, 8 no x loads,
                              // 16 no h flush), 0 in production
 };
 cudaError_t launch_lstm_seq2(const LstmSeq2Args& a, cudaStream_t s);
+bool lstm_seq2_fused_fc();     // did the most recent launch_lstm_seq2 include the output Linear?
 constexpr int kLstmSeqMinSteps = 2;  // single steps (streaming hops) stay on the FFMA recurrence
 constexpr int kLstmTcMinSeq = 128;   // below one full tile the FFMA recurrence is used
 int force_ffma();

@@ -25,9 +25,10 @@
 //    (ex2/rcp) -> h_t as bf16 hi/lo into the swizzled B operand -> fence.proxy.async -> arrive. No block-wide
 //    barrier inside the loop.
 //
-//   warps 0-15  cell update (one (unit, sequence) cell per lane and n8 half), h flush (fp32 rows or bf16 planes)
+//   warps 0-15  cell update (one (unit, sequence) cell per lane and n8 half)
 //   warps 16-19 weights -> TMEM once; x rows (global/L2) -> swizzled bf16 hi/lo B operand, 4 blocks ahead
-//   warp  20    tcgen05 issuer
+//   warps 20-21 tcgen05 issuers (one per gate-row tile); between steps they write the h rows of the previous step
+//               (fp32 rows or bf16 planes, half of the sequences each), fence and publish them
 #include <cstdlib>
 #include "kernels.cuh"
 #include "ptx.cuh"
@@ -49,8 +50,10 @@ constexpr int BLK = 4;           // steps per projection block (4 steps x 16 seq
 constexpr int NXB = 4;           // x-block buffers in shared memory
 constexpr int X_PLANE = BLK * SQ * 128;               // 8 KB: [64 (step, sequence) rows][64 k] bf16
 constexpr int H_PLANE = SQ * 128;                     // 2 KB: [16 sequences][64 k] bf16
-constexpr int OFF_X = 0, OFF_H = NXB * 2 * X_PLANE;
-constexpr int SMEM_BYTES = OFF_H + 2 * H_PLANE + 1024;
+constexpr int H_BUF = 2 * H_PLANE;                    // hi + lo
+constexpr int OFF_X = 0, OFF_H = NXB * 2 * X_PLANE;   // two h operand buffers: h_t lives in buffer (t + 1) % 2
+constexpr int FC_SMEM = 2 * 2 * 128 * 128 + 2 * kFeat * 128;          // fc role (below): two A blocks + the weight operand
+constexpr int SMEM_BYTES = (OFF_H + 2 * H_BUF > FC_SMEM ? OFF_H + 2 * H_BUF : FC_SMEM) + 1024;
 // tensor memory columns
 constexpr int COL_ACC = 0;       // [2 buffers][2 tiles][BLK steps][16 sequences] fp32
 constexpr int COL_WIH = 256;     // [2 tiles][2 planes][32]: lane = gate row, column = two consecutive k (bf16)
@@ -83,6 +86,172 @@ __device__ __forceinline__ int ld_acquire(const int* p) {
   return v;
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// Third CTA of a group (optional): the block's output Linear + residual, out = fc(h_layer1) + x (bsrnn.py:85-86 via
+// 119-120), riding the same wavefront: it consumes layer 1's fp32 rows a block of 128 (step, sequence) rows at a
+// time as layer 1 publishes them, one M = 128, N = 64, K = 64 split-bf16 tcgen05 tile per block (SS form), and
+// writes the fp32 feature rows of the next model block. Saves a separate GEMM launch over the whole batch and the
+// bf16-plane round trip of h; the CTA is idle most of the time (12 MMAs + 128 rows in and out per ~7 us).
+constexpr int FC_WARPS = 4;                              // loader / epilogue warps (TMEM lane quarters)
+constexpr int FC_THREADS = (FC_WARPS + 1) * 32;          // + issuer warp
+constexpr int FC_A_PLANE = 128 * 128;                    // [128 rows][64 k] bf16
+constexpr int FC_W_PLANE = kFeat * 128;                  // [64 n][64 k] bf16
+constexpr int FC_OFF_A = 0, FC_OFF_W = 2 * 2 * FC_A_PLANE;
+
+__device__ __forceinline__ void bar_fc() { asm volatile("bar.sync 2, %0;" ::"n"(FC_THREADS) : "memory"); }
+
+__device__ void fc_role(const LstmSeq2Args& a, int grp, uint8_t* smem_gen, uint32_t smem_base) {
+  __shared__ __align__(8) uint64_t bar_afull[2], bar_aempty[2], bar_accfull[2], bar_accfree[2];
+  __shared__ __align__(16) float fc_bias[kFeat];
+  __shared__ uint32_t fc_tmem_slot;
+  const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+  if (w > FC_WARPS) return;
+  const int sq = a.group, seq0 = grp * sq, T = a.nsteps;
+  const int spb = 128 / sq;                                // steps per block
+  const int nblk = (T + spb - 1) / spb;
+  if (tid == 0) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(smem_u32(&bar_afull[i]), FC_WARPS * 32);
+      mbar_init(smem_u32(&bar_aempty[i]), 1);
+      mbar_init(smem_u32(&bar_accfull[i]), 1);
+      mbar_init(smem_u32(&bar_accfree[i]), FC_WARPS * 32);
+    }
+    fence_mbar_init();
+  }
+  if (w == FC_WARPS) {
+    tmem_alloc(smem_u32(&fc_tmem_slot), 128);
+    tmem_relinquish();
+  } else {
+    // W_fc [64 n][64 k] fp32 -> bf16 hi/lo, K-major 128B-swizzled B operand; bias
+    for (int e = tid; e < kFeat * kFeat / 2; e += FC_WARPS * 32) {
+      const int n = e >> 5, k = (e & 31) * 2;
+      const float2 v = __ldg(reinterpret_cast<const float2*>(a.fcw + (long long)n * a.ldfcw + k));
+      uint32_t h, l;
+      split2(v.x, v.y, h, l);
+      const uint32_t off = (uint32_t)(n * 128 + (((k >> 3) ^ (n & 7)) << 4) + (k & 7) * 2);
+      *reinterpret_cast<uint32_t*>(smem_gen + FC_OFF_W + off) = h;
+      *reinterpret_cast<uint32_t*>(smem_gen + FC_OFF_W + FC_W_PLANE + off) = l;
+    }
+    if (tid < kFeat) fc_bias[tid] = __ldg(a.fcb + tid);
+    fence_proxy_async_smem();
+  }
+  tc_fence_before();
+  bar_fc();
+  tc_fence_after();
+  const uint32_t tmem_base = fc_tmem_slot;
+
+  if (w < FC_WARPS) {
+    const int lseq = tid >> 4, part = tid & 15;            // loader: (sequence, 4 floats at 4 part)
+    const int* flag = a.flags + a.ngroups + grp;           // layer 1's publications
+    // epilogue: this thread's TMEM lane = row r = (step in block r / sq, sequence r % sq)
+    const int r = tid, ei = r / sq, es = r - ei * sq;
+    const int eg = seq0 + es;
+    const bool evalid = eg < a.nseq;
+    const long long eoff = evalid ? (long long)(eg / a.n_inner) * a.outer + (long long)(eg % a.n_inner) * a.inner : 0;
+    const uint32_t tlane = tmem_base + ((uint32_t)(w * 32) << 16);
+    auto epilogue = [&](int b) {
+      mbar_wait(smem_u32(&bar_accfull[b & 1]), (uint32_t)((b >> 1) & 1));
+      tc_fence_after();
+      const int step = b * spb + ei;
+      const bool ok = evalid && step < T;
+      const float* res = a.x + eoff + (long long)step * a.step;
+      float* dst = a.fc_out + eoff + (long long)step * a.step;
+#pragma unroll 1
+      for (int half = 0; half < 2; ++half) {
+        uint32_t v[32];
+        tmem_ld_32x32(tlane + (uint32_t)((b & 1) * kFeat + half * 32), v);
+        tmem_ld_wait32(v);
+        if (ok) {
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const float4 x4 = __ldg(reinterpret_cast<const float4*>(res + half * 32 + q * 4));
+            const float4 b4 = *reinterpret_cast<const float4*>(&fc_bias[half * 32 + q * 4]);
+            float4 o;
+            o.x = __uint_as_float(v[4 * q + 0]) + b4.x + x4.x;
+            o.y = __uint_as_float(v[4 * q + 1]) + b4.y + x4.y;
+            o.z = __uint_as_float(v[4 * q + 2]) + b4.z + x4.z;
+            o.w = __uint_as_float(v[4 * q + 3]) + b4.w + x4.w;
+            *reinterpret_cast<float4*>(dst + half * 32 + q * 4) = o;
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(smem_u32(&bar_accfree[b & 1]));
+    };
+    for (int b = 0; b < nblk; ++b) {
+      const int need = min((b + 1) * spb, T);
+      if (lane == 0) {
+        while (ld_acquire(flag) < need) __nanosleep(200);
+      }
+      __syncwarp();
+      if (b >= 2) mbar_wait(smem_u32(&bar_aempty[b & 1]), (uint32_t)(((b >> 1) - 1) & 1));   // MMAs of block b-2 retired
+      uint8_t* a_hi = smem_gen + FC_OFF_A + (b & 1) * 2 * FC_A_PLANE;
+      uint8_t* a_lo = a_hi + FC_A_PLANE;
+#pragma unroll
+      for (int pass = 0; pass < 2; ++pass) {
+        float4 v[8];
+        int rows[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const int qq = pass * 8 + q;
+          const int s = sq == SQ ? (qq >> 3) * TS + lseq : lseq;
+          const int i = sq == SQ ? (qq & 7) : qq;
+          rows[q] = i * sq + s;
+          const int g = seq0 + s, step = b * spb + i;
+          v[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (g < a.nseq && step < T) {
+            const long long off = (long long)(g / a.n_inner) * a.outer + (long long)(g % a.n_inner) * a.inner + (long long)step * a.step;
+            v[q] = __ldcg(reinterpret_cast<const float4*>(a.hout + off + part * 4));
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          uint2 h, l;
+          split2(v[q].x, v[q].y, h.x, l.x);
+          split2(v[q].z, v[q].w, h.y, l.y);
+          const uint32_t off = (uint32_t)(rows[q] * 128 + (((part >> 1) ^ (rows[q] & 7)) << 4) + (part & 1) * 8);
+          *reinterpret_cast<uint2*>(a_hi + off) = h;
+          *reinterpret_cast<uint2*>(a_lo + off) = l;
+        }
+      }
+      fence_proxy_async_smem();
+      mbar_arrive(smem_u32(&bar_afull[b & 1]));
+      if (b > 0) epilogue(b - 1);
+    }
+    epilogue(nblk - 1);
+  } else {
+    const uint32_t idesc = make_idesc_bf16(128, kFeat);
+    const uint64_t w_hi = make_sw128_desc(smem_base + FC_OFF_W);
+    const uint64_t w_lo = make_sw128_desc(smem_base + FC_OFF_W + FC_W_PLANE);
+    for (int b = 0; b < nblk; ++b) {
+      mbar_wait(smem_u32(&bar_afull[b & 1]), (uint32_t)((b >> 1) & 1));
+      if (b >= 2) mbar_wait(smem_u32(&bar_accfree[b & 1]), (uint32_t)(((b >> 1) - 1) & 1));
+      tc_fence_after();
+      if (elect_one()) {
+        const uint64_t a_hi = make_sw128_desc(smem_base + FC_OFF_A + (b & 1) * 2 * FC_A_PLANE);
+        const uint64_t a_lo = make_sw128_desc(smem_base + FC_OFF_A + (b & 1) * 2 * FC_A_PLANE + FC_A_PLANE);
+        const uint32_t d = tmem_base + (uint32_t)((b & 1) * kFeat);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+          const uint64_t adv = (uint64_t)(kk * 32 >> 4);
+          mma_bf16_ss(d, a_lo + adv, w_hi + adv, idesc, kk != 0);   // small terms first
+          mma_bf16_ss(d, a_hi + adv, w_lo + adv, idesc, 1);
+          mma_bf16_ss(d, a_hi + adv, w_hi + adv, idesc, 1);
+        }
+        mma_commit(smem_u32(&bar_accfull[b & 1]));
+        mma_commit(smem_u32(&bar_aempty[b & 1]));
+      }
+      __syncwarp();
+    }
+  }
+  tc_fence_before();
+  bar_fc();
+  if (w == FC_WARPS) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 128);
+  }
+}
+
 __global__ void __launch_bounds__(THREADS, 1)
 lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
   extern __shared__ uint8_t smem_raw[];
@@ -92,7 +261,13 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
 
   const int tid = threadIdx.x;
   const int w = tid >> 5, lane = tid & 31;
-  const int layer = blockIdx.x & 1, grp = blockIdx.x >> 1;
+  const int nrole = a.fuse_fc ? 3 : 2;
+  const int layer = blockIdx.x % nrole, grp = blockIdx.x / nrole;      // role 0/1 = LSTM layer, 2 = output Linear
+  const uint32_t smem_base0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  if (layer == 2) {
+    fc_role(a, grp, smem_raw + (smem_base0 - smem_u32(smem_raw)), smem_base0);
+    return;
+  }
   const int sq = a.group;          // sequences this CTA really owns: 16, or 8 (only fragment 0) when that still fits the SMs
   const int seq0 = grp * sq;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -101,7 +276,9 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
   const int nblk = (T + BLK - 1) / BLK;
   const float* xin = layer ? a.hmid : a.x;
   float* out = layer ? a.hout : a.hmid;
-  void* planes = layer ? a.hplanes : nullptr;
+  void* planes = (layer && !a.fuse_fc) ? a.hplanes : nullptr;
+  const bool publish = layer == 0 || a.fuse_fc;          // somebody downstream in this launch reads this layer's rows
+  int* my_flag = a.flags + layer * a.ngroups + grp;       // rows of steps < *my_flag of this group are in global memory
 
   if (tid == 0) {
     for (int i = 0; i < NXB; ++i) {
@@ -148,6 +325,8 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
       split1(h0, hh, hl);
       *reinterpret_cast<uint16_t*>(smem_gen + OFF_H + hoffs[j]) = hh;
       *reinterpret_cast<uint16_t*>(smem_gen + OFF_H + H_PLANE + hoffs[j]) = hl;
+      *reinterpret_cast<uint16_t*>(smem_gen + OFF_H + H_BUF + hoffs[j]) = 0;
+      *reinterpret_cast<uint16_t*>(smem_gen + OFF_H + H_BUF + H_PLANE + hoffs[j]) = 0;
     }
     fence_proxy_async_smem();
   } else if (w < MMA_WARP) {
@@ -185,30 +364,6 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
     const float b_lo = __ldg(a.bias[layer] + w * 16 + gr), b_hi = __ldg(a.bias[layer] + w * 16 + gr + 8);
     float* hNp = a.hN[layer];
     float* cNp = a.cN[layer];
-    // h writer role of the first 256 threads: (sequence tid/16, 4 floats at 4*(tid%16))
-    const int lseq = (tid >> 4) & (SQ - 1), part = tid & 15;
-    const int lg = seq0 + lseq;
-    const bool lvalid = tid < sq * 16 && lg < a.nseq;
-    const long long hoff = lvalid ? (long long)(lg / a.n_inner) * a.outer + (long long)(lg % a.n_inner) * a.inner : 0;
-    auto flush = [&](int t) {
-      if (!lvalid || (a.exp & 16)) return;
-      const float4 v = *reinterpret_cast<const float4*>(&hF[t % 3][lseq][part * 4]);
-      if (planes != nullptr) {
-        // A operand of the Linear that follows (kernels.cuh planes: [m-tile][32-column chunk][128 x 64 B]): row =
-        // output row index, columns 4 part .. +3 as bf16 hi and lo
-        const long long m = (hoff + (long long)t * a.step) >> 6;
-        const int r = (int)(m & 127);
-        uint8_t* p = reinterpret_cast<uint8_t*>(planes) + ((m >> 7) * 2 + (part >> 3)) * (2 * kPlaneBlock) +
-                     sw64(r, (part & 7) >> 1) + (part & 1) * 8;
-        uint2 h, l;
-        split2(v.x, v.y, h.x, l.x);
-        split2(v.z, v.w, h.y, l.y);
-        *reinterpret_cast<uint2*>(p) = h;
-        *reinterpret_cast<uint2*>(p + a.hp_lo) = l;
-      } else {
-        *reinterpret_cast<float4*>(out + hoff + (long long)t * a.step + part * 4) = v;
-      }
-    };
     // pre-activations of fragment j -> cell update, h to the B operand and the staging row
     auto cell = [&](const float (&g)[4], int j, int t) {
       const float acc0 = g[0] + b_lo, acc1 = g[1] + b_lo, acc2 = g[2] + b_hi, acc3 = g[3] + b_hi;
@@ -225,8 +380,11 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
       const float h = (1.f - ec) * rcp_approx((1.f + eo) * (1.f + ec));
       uint16_t hh, hl;
       split1(h, hh, hl);
-      *reinterpret_cast<uint16_t*>(smem_gen + OFF_H + hoffs[j]) = hh;
-      *reinterpret_cast<uint16_t*>(smem_gen + OFF_H + H_PLANE + hoffs[j]) = hl;
+      // the MMAs of step t (either tile's, possibly not even issued yet by the other issuer warp) read h_{t-1} from
+      // the other buffer: no write-after-read hazard, whatever the skew between the two issuers
+      uint8_t* hb = smem_gen + OFF_H + ((t + 1) & 1) * H_BUF;
+      *reinterpret_cast<uint16_t*>(hb + hoffs[j]) = hh;
+      *reinterpret_cast<uint16_t*>(hb + H_PLANE + hoffs[j]) = hl;
       hF[t % 3][j * TS + sl][unit] = h;
       if (t == T - 1 && valid[j] && hNp != nullptr) {
         const int gseq = seq0 + j * TS + sl;
@@ -239,6 +397,31 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
 #ifdef BSB_SEQ2_TRACE
     long long* tr = (blockIdx.x < 2 && w == 0 && lane == 0) ? &g_seq2_trace[blockIdx.x][0][0][0] : nullptr;
 #endif
+    // h rows leave one step late, after this warp's arrive: thread tid owns (sequence tid / 16, 16-byte part tid % 16)
+    const int fseq = (tid >> 4) & 15, fpart = tid & 15;
+    const int fg = seq0 + fseq;
+    const bool fvalid = tid < sq * 16 && fg < a.nseq && !(a.exp & 16);
+    const long long frow = fvalid ? (long long)(fg / a.n_inner) * a.outer + (long long)(fg % a.n_inner) * a.inner : 0;
+    auto flush = [&](int t) {
+      if (!fvalid) return;
+      const long long hoff = frow + (long long)t * a.step;
+      const float4 v = *reinterpret_cast<const float4*>(&hF[t % 3][fseq][fpart * 4]);
+      if (planes != nullptr) {
+        // A operand of the Linear that follows (kernels.cuh planes: [m-tile][32-column chunk][128 x 64 B]): row =
+        // output row index, columns 4 part .. +3 as bf16 hi and lo
+        const long long m = hoff >> 6;
+        const int r = (int)(m & 127);
+        uint8_t* p = reinterpret_cast<uint8_t*>(planes) + ((m >> 7) * 2 + (fpart >> 3)) * (2 * kPlaneBlock) +
+                     sw64(r, (fpart & 7) >> 1) + (fpart & 1) * 8;
+        uint2 h, l;
+        split2(v.x, v.y, h.x, l.x);
+        split2(v.z, v.w, h.y, l.y);
+        *reinterpret_cast<uint2*>(p) = h;
+        *reinterpret_cast<uint2*>(p + a.hp_lo) = l;
+      } else {
+        *reinterpret_cast<float4*>(out + hoff + fpart * 4) = v;
+      }
+    };
     for (int t = 0; t < T; ++t) {
       TR(0);
       mbar_wait(smem_u32(&bar_gates[w >> 3]), (uint32_t)(t & 1));    // (polling with test_wait measured slower)
@@ -260,24 +443,25 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&bar_h));
       TR(4);
-      // rows of step t-1 go out while the tensor core works on step t+1 (complete since bar_gates(t); the staging
-      // buffer is reused by step t+2, which nobody reaches before this warp's next arrive)
+      // off the chain: rows of step t-1 (every cell warp wrote its units before its arrive on bar_h(t-1), which the
+      // gates of step t waited for)
       if (t > 0) flush(t - 1);
-      TR(5);
-      // bar_gates(t) implied every warp's arrive for h_{t-1}, and before that arrive every warp had flushed step
-      // t-3: rows of steps < t-2 are on their way to L2. Published by a thread with no rows to flush.
-      if (layer == 0 && tid == NT - 32 && t > 2 && ((t - 2) % BLK) == 0) {
+      // Publication of the rows of steps < t-2, every BLK steps: every cell warp ran flush(t-3) before its arrive on
+      // bar_h(t-1) in program order, and this thread has observed the gates of step t, i.e. all those arrives
+      // (release/acquire at CTA scope through the mbarriers; the device-scope fence below is cumulative over them).
+      if (publish && tid == 0 && t > 2 && ((t - 2) % BLK) == 0) {
         __threadfence();
-        *reinterpret_cast<volatile int*>(a.flags + grp) = t - 2;
+        *reinterpret_cast<volatile int*>(my_flag) = t - 2;
       }
     }
+    // last rows: cell warps only (named barrier 1), then one thread publishes everything
     bar_cells();
     flush(T - 1);
-    if (layer == 0) {
+    if (publish) {
       bar_cells();
       if (tid == 0) {
         __threadfence();
-        *reinterpret_cast<volatile int*>(a.flags + grp) = T;
+        *reinterpret_cast<volatile int*>(my_flag) = T;
       }
     }
   } else if (w < MMA_WARP) {
@@ -293,7 +477,7 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
       xptr[s2] = xin;
       if (lvalid[s2]) xptr[s2] += (long long)(lg / a.n_inner) * a.outer + (long long)(lg % a.n_inner) * a.inner + part * 4;
     }
-    const int* flag = a.flags + grp;
+    const int* flag = a.flags + grp;               // layer 0's publications
     for (int b = 0; b < nblk; ++b) {            // 4 steps x 16 sequences x 64 floats -> planes of buffer b % NXB
       if (b >= NXB) mbar_wait(smem_u32(&bar_xempty[b % NXB]), ((b / NXB) - 1) & 1);   // MMAs of block b - NXB retired
       uint8_t* x_hi = smem_gen + OFF_X + (b % NXB) * 2 * X_PLANE;
@@ -336,8 +520,8 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
     const int tile = w - MMA_WARP;
     const uint32_t idesc_x = make_idesc_bf16(128, BLK * SQ);
     const uint32_t idesc_h = make_idesc_bf16(128, SQ);
-    const uint64_t h_hi = make_sw128_desc(smem_base + OFF_H);
-    const uint64_t h_lo = make_sw128_desc(smem_base + OFF_H + H_PLANE);
+    const uint64_t h_hi0 = make_sw128_desc(smem_base + OFF_H);
+    const uint64_t h_lo0 = make_sw128_desc(smem_base + OFF_H + H_PLANE);
     const uint32_t wih_hi = tmem_base + (uint32_t)(COL_WIH + (tile * 2 + 0) * 32), wih_lo = wih_hi + 32;
     const uint32_t whh_hi = tmem_base + (uint32_t)(COL_WHH + (tile * 2 + 0) * 32), whh_lo = whh_hi + 32;
     // W_ih'[tile] . x_block^T -> accumulator buffer b % 2 (overwrites: the block two back is consumed). ~50 cycles per
@@ -375,6 +559,8 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
       if (elect_one()) {
         if (!(a.exp & 2)) {
           const uint32_t d = tmem_base + (uint32_t)(COL_ACC + ((t / BLK) & 1) * (2 * BLK * SQ) + tile * (BLK * SQ) + (t % BLK) * SQ);
+          const uint64_t hsel = (uint64_t)((t & 1) * (H_BUF >> 4));      // h_{t-1} is in buffer t % 2
+          const uint64_t h_hi = h_hi0 + hsel, h_lo = h_lo0 + hsel;
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {
             const uint64_t adv = (uint64_t)(kk * 32 >> 4);
@@ -410,6 +596,9 @@ extern "C" int bsb_debug_seq2_trace(long long* host, int n) {
 }
 #endif
 
+static int g_last_fused = 0;
+bool lstm_seq2_fused_fc() { return g_last_fused != 0; }
+
 cudaError_t launch_lstm_seq2(const LstmSeq2Args& a, cudaStream_t s) {
   if (a.nseq <= 0 || a.nsteps <= 0) return cudaSuccess;
   static bool attr_set = false;
@@ -422,15 +611,24 @@ cudaError_t launch_lstm_seq2(const LstmSeq2Args& a, cudaStream_t s) {
   if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   // 8 sequences per CTA halve the cell update of a step (one fragment per lane instead of two); taken when all
   // CTAs are still co-resident, i.e. for short batches and long-form clips (cfg 1, 3, 5)
-  const int group = 2 * ((a.nseq + TS - 1) / TS) <= sms ? TS : SQ;
+  const int g8 = (a.nseq + TS - 1) / TS, g16 = (a.nseq + SQ - 1) / SQ;
+  const bool can_fuse = a.fcw != nullptr && a.fc_out != nullptr && a.fc_out != a.x && !(std::getenv("BSB_SEQ2_NOFC"));
+  // preference: fused output Linear (third CTA per group) as long as all CTAs are co-resident, small groups first
+  int group = SQ, fuse = 0;
+  if (can_fuse && 3 * g8 <= sms) { group = TS; fuse = 1; }
+  else if (2 * g8 <= sms) { group = TS; }
+  else if (can_fuse && 3 * g16 <= sms) { fuse = 1; }
   const int groups = (a.nseq + group - 1) / group;
   static const int exp_mode = std::getenv("BSB_SEQ2_EXP") ? std::atoi(std::getenv("BSB_SEQ2_EXP")) : 0;
   LstmSeq2Args b = a;
   b.exp = exp_mode;
-  b.group = (exp_mode & 128) ? SQ : group;
-  cudaError_t e = cudaMemsetAsync(a.flags, 0, sizeof(int) * groups, s);
+  b.group = group;
+  b.fuse_fc = fuse;
+  b.ngroups = groups;
+  cudaError_t e = cudaMemsetAsync(a.flags, 0, sizeof(int) * 2 * groups, s);
   if (e != cudaSuccess) return e;
-  lstm_seq2_kernel<<<2 * groups, THREADS, SMEM_BYTES, s>>>(b);
+  lstm_seq2_kernel<<<(fuse ? 3 : 2) * groups, THREADS, SMEM_BYTES, s>>>(b);
+  g_last_fused = fuse;
   count_launch();
   return cudaGetLastError();
 }
