@@ -8,7 +8,9 @@ from .bsrnn import (BSRNN, BandwiseLSTM, NormRNNResidual, TimewiseLSTM, Trainabl
 from .wrap import (BatchSeparator, StreamingSeparator, infer, metrics_from_stats, pair_stats, stft_pack, train_infer,
                    unpack_istft)
 from .shard import shard_range, aggregate_throughput
+from .export import ToTrace, trace_streaming_step          # registers the bsrnn_b200:: operators
 
 __all__ = ["BSRNN", "BandwiseLSTM", "TimewiseLSTM", "NormRNNResidual", "TrainableConstantModule",
            "generate_bandsplits", "band_features", "merge_channels", "stft_pack", "unpack_istft", "infer",
-           "StreamingSeparator", "BatchSeparator", "pair_stats", "metrics_from_stats", "train_infer", "shard_range", "aggregate_throughput"]
+           "StreamingSeparator", "BatchSeparator", "pair_stats", "metrics_from_stats", "train_infer", "shard_range", "aggregate_throughput",
+           "ToTrace", "trace_streaming_step"]

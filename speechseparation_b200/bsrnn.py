@@ -194,6 +194,11 @@ class BSRNN(nn.Module):
         self._check_input(x, 3, "x")
         if x.shape[2] < 1:
             raise RuntimeError("x: empty time axis")
+        if torch.jit.is_tracing():             # export path: a recordable operator (export.py)
+            from . import export
+            with torch.no_grad():
+                packed = self.packed_weights(x.device)
+            return export.forward_op(x, packed)
         if self._needs_grad(x):
             return _ForwardOnly.apply(self, x, *self.parameters())
         return self._forward_impl(x)
@@ -221,6 +226,12 @@ class BSRNN(nn.Module):
             raise RuntimeError(f"state must have shape (4, 2, {C * 12}, {band_features}) for {C} rows, got {shape}")
         if state.device != x.device or state.dtype != torch.float32:
             raise RuntimeError("state must be float32 on the same CUDA device as x")
+        if torch.jit.is_tracing():             # export path (infer-streaming.py:20-28,74): a recordable operator
+            from . import export
+            with torch.no_grad():
+                packed = self.packed_weights(x.device)
+            y, new_state = export.forward_recurrent_op(x, state, packed)
+            return y, new_state
         if self._needs_grad(x, state):
             raise NotImplementedError("speechseparation_b200.BSRNN.forward_recurrent is forward-only; "
                                       "call it under torch.no_grad()")

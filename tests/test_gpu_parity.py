@@ -490,3 +490,40 @@ def test_long_form_cfg5_shape(dev, model, oracle_sd):
     out = model.separate(wav.to(dev))
     assert out.shape == ref.shape == (1, 1024 * 2583)
     assert O.max_rel_err(out.cpu(), ref) < GATE / 5
+
+
+def test_traced_streaming_step_records_the_operator_and_replays(dev, model, golden_dir, tmp_path):
+    """the reference exports by tracing ToTrace(model) (infer-streaming.py:20-28,57-74). The trace
+    must hold the step as ONE recordable operator, survive torch.jit.save/load, and reproduce the eager C-ABI call
+    bit for bit on the golden hops (state carried by the caller)."""
+    from speechseparation_b200 import ToTrace, trace_streaming_step
+    traced = trace_streaming_step(model, rows=2, device=dev)
+    kinds = [n.kind() for n in traced.graph.nodes()]
+    assert kinds.count("bsrnn_b200::forward_recurrent") == 1, kinds
+    path = os.path.join(tmp_path, "model-script.pth")
+    torch.jit.save(traced, path)
+    loaded = torch.jit.load(path, map_location=dev)
+    g = np.load(os.path.join(golden_dir, "recurrent_small.npz"))
+    s_e = s_t = s_l = torch.from_numpy(g["state0"]).to(dev)
+    for h in range(g["x"].shape[0]):
+        x = torch.from_numpy(g["x"][h]).to(dev)
+        y_e, s_e = model.forward_recurrent(x, s_e)
+        y_t, s_t, empty = traced(x, s_t)
+        y_l, s_l, _ = loaded(x, s_l)
+        assert empty.numel() == 0                                     # the reference's third, empty output
+        assert torch.equal(y_t, y_e) and torch.equal(s_t, s_e)
+        assert torch.equal(y_l, y_e) and torch.equal(s_l, s_e)
+        assert rel(y_t, torch.from_numpy(g["y"][h])) < STAGE_TOL
+    # the eager wrapper behaves like the reference's ToTrace outside a trace too
+    a, b, c = ToTrace(model)(torch.from_numpy(g["x"][0]).to(dev), torch.from_numpy(g["state0"]).to(dev))
+    assert a.shape == (2, 2050) and b.shape == (4, 2, 24, 64) and c.numel() == 0
+
+
+def test_traced_offline_forward_replays(dev, model, golden_dir):
+    g = np.load(os.path.join(golden_dir, "offline_small.npz"))
+    x = torch.from_numpy(g["x"]).to(dev)
+    with torch.no_grad():
+        traced = torch.jit.trace(model, (x,), check_trace=False)
+    assert [n.kind() for n in traced.graph.nodes()].count("bsrnn_b200::forward") == 1
+    assert torch.equal(traced(x), model.forward(x))
+    assert rel(traced(x), torch.from_numpy(g["y"])) < STAGE_TOL

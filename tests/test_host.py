@@ -194,3 +194,20 @@ def test_plugin_argument_errors_and_weight_file(tmp_path, oracle_sd):
     assert (w[:first.size] == first).all()
     with pytest.raises(RuntimeError):
         plugin.flat_weights({"a": torch.zeros(3)})
+
+
+def test_export_operators_registered_with_shapes_and_no_cpu_kernel():
+    """SURVEY 8(f) row 3: the two model entry points exist as torch.library operators (what a tracer records);
+    shape propagation works without a device and there is no CPU kernel behind them."""
+    import speechseparation_b200  # noqa: F401  (registers the operators)
+    s = str(torch.ops.bsrnn_b200.forward_recurrent.default._schema)
+    assert s == "bsrnn_b200::forward_recurrent(Tensor x, Tensor state, Tensor packed) -> (Tensor, Tensor)"
+    assert str(torch.ops.bsrnn_b200.forward.default._schema) == "bsrnn_b200::forward(Tensor x, Tensor packed) -> Tensor"
+    x, st, pk = (torch.empty(s, device="meta") for s in ((2, 2050), (4, 2, 24, 64), (16,)))
+    y, ns = torch.ops.bsrnn_b200.forward_recurrent(x, st, pk)
+    assert y.shape == (2, 2050) and ns.shape == (4, 2, 24, 64)
+    assert torch.ops.bsrnn_b200.forward(torch.empty(3, 2050, 7, device="meta"), pk).shape == (3, 2050, 7)
+    with pytest.raises(NotImplementedError):
+        torch.ops.bsrnn_b200.forward_recurrent(torch.zeros(2, 2050), torch.zeros(4, 2, 24, 64), torch.zeros(16))
+    with pytest.raises(NotImplementedError):
+        torch.ops.bsrnn_b200.forward(torch.zeros(1, 2050, 2), torch.zeros(16))
