@@ -199,7 +199,9 @@ __device__ __forceinline__ void warp_fft1024(float2 (&v)[32], float2* tr, const 
   fft32<INV>(v);
 }
 
-__global__ void __launch_bounds__(kFrameWarps * 32, 4)
+// 5 CTAs (20 warps) per SM: 96 registers with 52 bytes of spill beats 128 registers at 16 warps (88.6 -> 79.6 us at
+// cfg 2: the kernel waits on its frame loads, more resident warps hide them; 6 CTAs = 80 registers spills 400 bytes: 131 us)
+__global__ void __launch_bounds__(kFrameWarps * 32, 5)
 stft_warp_kernel(const float* __restrict__ wav, long long L, int T, int nrows, const float* __restrict__ win,
                  const float2* __restrict__ tw, float* __restrict__ xf, int xs) {
   __shared__ __align__(16) float2 tr_all[kFrameWarps][32 * kTr];
