@@ -9,6 +9,8 @@
 // and the final "x * mask" (bsrnn.py:441) are fused into the epilogue.
 #include "kernels.cuh"
 
+#include <cstdlib>
+
 namespace bsb {
 
 long long g_launches = 0;
@@ -164,7 +166,97 @@ grouped_linear_kernel(const __grid_constant__ GroupedArgs args) {
   }
 }
 
+// ---- small-M variant (streaming hops: M = rows of one frame, 1..32) ----------------------------------------
+// With a handful of rows the layer is a weight read: 4.2 MB of fp32 weights for a d x d layer against 2 x 2050
+// activations. The tiled kernel above walks K serially in 16-wide steps behind block barriers with 12 CTAs on its
+// largest band (51 us per d x d layer at 2 rows); here a warp owns GV_COLS output columns, its lanes stride over K
+// with 16-byte weight loads (one 512-byte run per row and iteration), the <= 8 activation rows of the CTA sit in
+// shared memory, and the partial sums meet in a shuffle reduction. CTA = 8 warps = 16 columns of one band x 8 rows.
+constexpr int GV_WARPS = 8, GV_COLS = 2, GV_MR = 8, GV_BN = GV_WARPS * GV_COLS;
+constexpr int GV_KMAX = 768;                       // widest band (kMaxBandD); checked by the launcher
+
+__global__ void __launch_bounds__(GV_WARPS * 32)
+grouped_gemv_kernel(const __grid_constant__ GroupedArgs args) {
+  __shared__ __align__(16) float As[GV_MR][GV_KMAX];
+  const int tile = blockIdx.x;
+  int pi = 0;
+  while (pi + 1 < args.nprob && tile >= args.p[pi + 1].tile_start) ++pi;
+  const LinProb& P = args.p[pi];
+  const int local = tile - P.tile_start;
+  const int m0 = (local / P.tiles_n) * GV_MR;
+  const int n0 = (local % P.tiles_n) * GV_BN;
+  const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+  const int M = P.M, K = P.K, N = P.N, ldw = P.ldw;
+  const int Kp = (K + 127) & ~127;                 // a warp covers 128 k per iteration
+  const float* __restrict__ A = P.A;
+  for (int e = tid; e < GV_MR * Kp; e += GV_WARPS * 32) {
+    const int r = e / Kp, k = e - r * Kp;
+    As[r][k] = (m0 + r < M && k < K) ? __ldg(A + (long long)(m0 + r) * P.lda + k) : 0.f;
+  }
+  __syncthreads();
+  const int nw = n0 + w * GV_COLS;
+  float acc[GV_COLS][GV_MR];
+#pragma unroll
+  for (int c = 0; c < GV_COLS; ++c)
+#pragma unroll
+    for (int r = 0; r < GV_MR; ++r) acc[c][r] = 0.f;
+  const float* __restrict__ W = P.W + (long long)nw * ldw;        // rows exist up to Npad (multiple of 64)
+#pragma unroll 3
+  for (int k = lane * 4; k < Kp; k += 128) {
+    float4 wv[GV_COLS];
+#pragma unroll
+    for (int c = 0; c < GV_COLS; ++c)
+      wv[c] = k < ldw ? __ldg(reinterpret_cast<const float4*>(W + (long long)c * ldw + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int r = 0; r < GV_MR; ++r) {
+      const float4 av = *reinterpret_cast<const float4*>(&As[r][k]);
+#pragma unroll
+      for (int c = 0; c < GV_COLS; ++c) {
+        acc[c][r] = fmaf(av.x, wv[c].x, acc[c][r]);
+        acc[c][r] = fmaf(av.y, wv[c].y, acc[c][r]);
+        acc[c][r] = fmaf(av.z, wv[c].z, acc[c][r]);
+        acc[c][r] = fmaf(av.w, wv[c].w, acc[c][r]);
+      }
+    }
+  }
+  float mine = 0.f;                                // lane c * 8 + r keeps the sum of (column c, row r)
+#pragma unroll
+  for (int c = 0; c < GV_COLS; ++c)
+#pragma unroll
+    for (int r = 0; r < GV_MR; ++r) {
+      float v = acc[c][r];
+#pragma unroll
+      for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == c * GV_MR + r) mine = v;
+    }
+  if (lane >= GV_COLS * GV_MR) return;
+  const int n = nw + lane / GV_MR, m = m0 + lane % GV_MR;
+  if (n >= N || m >= M) return;
+  float t = mine + __ldg(P.bias + n);
+  if (P.act == ACT_LRELU) t = lrelu(t);
+  if (P.res != nullptr) t += P.res[(long long)m * P.ldres + n];
+  if (P.mul != nullptr) t *= P.mul[(long long)m * P.ldmul + n];
+  P.O[(long long)m * P.ldo + n] = t;
+}
+
 }  // namespace
+
+constexpr int kGemvMaxRows = 32;
+
+cudaError_t launch_gemv_grouped_linear(GroupedArgs& args, cudaStream_t s) {
+  int total = 0;
+  for (int i = 0; i < args.nprob; ++i) {
+    LinProb& P = args.p[i];
+    P.tile_start = total;
+    P.tiles_n = (P.N + GV_BN - 1) / GV_BN;
+    total += P.tiles_n * ((P.M + GV_MR - 1) / GV_MR);
+  }
+  args.total_tiles = total;
+  if (total == 0) return cudaSuccess;
+  grouped_gemv_kernel<<<total, GV_WARPS * 32, 0, s>>>(args);
+  count_launch();
+  return cudaGetLastError();
+}
 
 cudaError_t launch_ffma_grouped_linear(GroupedArgs& args, cudaStream_t s) {
   int total = 0;
@@ -190,7 +282,13 @@ cudaError_t launch_grouped_linear(GroupedArgs& args, cudaStream_t s) {
   bool tc = !g_force_ffma && args.nprob > 0;
   for (int i = 0; i < args.nprob; ++i)
     if (args.p[i].K > 0 && (args.p[i].M < kTcMinRows || args.p[i].Wh == nullptr)) tc = false;
-  if (!tc) return launch_ffma_grouped_linear(args, s);
+  if (!tc) {
+    static const bool no_gemv = getenv("BSB_NO_GEMV") != nullptr;      // A/B switch
+    bool gemv = args.nprob > 0 && !no_gemv;
+    for (int i = 0; i < args.nprob; ++i)
+      if (args.p[i].M > kGemvMaxRows || args.p[i].K > GV_KMAX || args.p[i].O == nullptr || (args.p[i].K > 0 && args.p[i].A == nullptr)) gemv = false;
+    return gemv ? launch_gemv_grouped_linear(args, s) : launch_ffma_grouped_linear(args, s);
+  }
   cudaError_t e = launch_tc_grouped_linear(args, s);
   if (e != cudaSuccess) return e;
   GroupedArgs rest{};                       // K == 0 problems: out = bias broadcast
