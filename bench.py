@@ -358,10 +358,23 @@ def main():
         if f"rnn{j}.fc" not in stage_ms and f"rnn{j}.rec" in stage_ms:
             flops[f"rnn{j}.rec"] += flops[f"rnn{j}.fc"]
             byt[f"rnn{j}.rec"] += byt[f"rnn{j}.fc"] - 2 * 12 * 64 * 4      # h of layer 1 no longer leaves and re-enters as planes
+    stage_kernel = dict(STAGE_KERNEL)
+    for j in (0, 2):                       # band-axis block below the tensor-core recurrence's row threshold: fc_in and
+        if f"rnn{j}.proj0" in stage_ms:    # the W_ih projections are GEMM launches, the recurrence runs in lstm_rec_kernel
+            nd = 2
+            p0, p1 = 2.0 * 12 * (64 * 64 + 64 * 256 * nd), 2.0 * 12 * (64 * nd * 256 * nd)
+            flops[f"rnn{j}.proj0"], flops[f"rnn{j}.proj1"] = p0, p1
+            flops[f"rnn{j}.rec0"] -= p0
+            flops[f"rnn{j}.rec1"] -= p1
+            byt[f"rnn{j}.proj0"] = 3072 * 2 + 12 * 256 * nd * 4          # features in, fc_in out, gate rows out
+            byt[f"rnn{j}.proj1"] = 12 * (64 * nd + 256 * nd) * 4
+            byt[f"rnn{j}.rec0"] = byt[f"rnn{j}.rec1"] = 12 * (256 * nd + 64 * nd) * 4
+            stage_kernel[f"rnn{j}.proj0"], stage_kernel[f"rnn{j}.proj1"] = (GEMM, 2), (GEMM, 1)
+            stage_kernel[f"rnn{j}.rec0"] = stage_kernel[f"rnn{j}.rec1"] = ("lstm_rec_kernel", 1)
     total_ms = sum(stage_ms.values())
     kern = {}
     for st_name, ms in stage_ms.items():
-        kname, nl = STAGE_KERNEL[st_name]
+        kname, nl = stage_kernel[st_name]
         k = kern.setdefault(kname, {"ms": 0.0, "launches": 0, "flops": 0.0, "bytes": 0.0})
         k["ms"] += ms
         k["launches"] += nl

@@ -360,7 +360,8 @@ int run_rnn_block(int j, const float* fin, int C, int T, const void* packed, con
   const long long rows = (long long)C * T * kBands;
   const int ldx = kGates * R.ndir, ldh = kFeat * R.ndir;
   char nm[40];
-  if (band && (long long)C * T >= kLstmTcMinSeq && !force_ffma()) {
+  static const long long tc_min_seq = getenv("BSB_LSTM_TC_MIN") ? atoll(getenv("BSB_LSTM_TC_MIN")) : kLstmTcMinSeq;
+  if (band && (long long)C * T >= tc_min_seq && !force_ffma()) {
     // tensor-core path: fc_in and the W_ih projections are fused into the layer kernels (lstm_tc.cu)
     float* hl[2] = {w.hbuf, w.xproj};                 // layer outputs [rows][128] (xproj is free here)
     for (int layer = 0; layer < 2; ++layer) {

@@ -131,7 +131,11 @@ struct LstmSeq2Args {
 cudaError_t launch_lstm_seq2(const LstmSeq2Args& a, cudaStream_t s);
 bool lstm_seq2_fused_fc();     // did the most recent launch_lstm_seq2 include the output Linear?
 constexpr int kLstmSeqMinSteps = 2;  // single steps (streaming hops) stay on the FFMA recurrence
-constexpr int kLstmTcMinSeq = 128;   // below one full tile the FFMA recurrence is used
+// Band-axis blocks below this many sequences (frame-rows) run as GEMM projections + the FFMA recurrence: the tcgen05
+// layer kernel puts 128 sequences on one CTA for ~66-80 us whatever the count, so 128 rows = 2 CTAs on 148 SMs.
+// Measured crossover (hop of R rows, device ms, tcgen05 vs split): 128: 0.61/0.50, 256: 0.65/0.54, 512: 0.74/0.67,
+// 1024: 0.87/0.94; cfg 1 (346 frame-rows): 1.06/0.99 ms. Override for A/B runs: env BSB_LSTM_TC_MIN.
+constexpr int kLstmTcMinSeq = 768;
 int force_ffma();
 
 // ------------------------------------------------------------------------------------

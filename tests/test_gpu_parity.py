@@ -299,10 +299,12 @@ def _run_block(l, j, fin, C, T, packed, ws, state_in=None, state_out=None):
     return fout
 
 
-@pytest.mark.parametrize("C,T", [(1, 128), (3, 131), (2, 300), (7, 64)])
+@pytest.mark.parametrize("C,T", [(1, 768), (3, 257), (2, 450), (7, 128), (1, 128), (3, 131), (2, 300), (7, 64)])
 def test_band_axis_tensor_core_lstm_vs_oracle(dev, model, oracle_sd, C, T):
-    """BandwiseLSTM blocks (bsrnn.py:138-153) on the tcgen05 kernel (C*T >= 128 sequences; ragged last
-    tile at 393 and 448+... rows) against the ATen LSTM of the oracle and the fp32 FFMA kernels."""
+    """BandwiseLSTM blocks (bsrnn.py:138-153) against the ATen LSTM of the oracle and the fp32 FFMA kernels: on the
+    tcgen05 recurrence kernel (C*T >= 768 sequences; ragged last tile at 771, 900 and 896 rows), and below that on
+    tensor-core projections + the FFMA recurrence (128..600 sequences: few 128-row tiles would leave the GPU to
+    2-10 CTAs walking 12 steps)."""
     from speechseparation_b200 import _lib
     l = _lib.lib()
     packed = model.packed_weights(dev)
