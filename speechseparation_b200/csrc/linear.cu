@@ -166,7 +166,7 @@ grouped_linear_kernel(const __grid_constant__ GroupedArgs args) {
   }
 }
 
-// ---- small-M variant (streaming hops: M = rows of one frame, 1..32) ----------------------------------------
+// ---- small-M variant (streaming hops: M = rows of one frame, 1..127) ----------------------------------------
 // With a handful of rows the layer is a weight read: 4.2 MB of fp32 weights for a d x d layer against 2 x 2050
 // activations. The tiled kernel above walks K serially in 16-wide steps behind block barriers with 12 CTAs on its
 // largest band (51 us per d x d layer at 2 rows); here a warp owns GV_COLS output columns, its lanes stride over K
@@ -241,7 +241,9 @@ grouped_gemv_kernel(const __grid_constant__ GroupedArgs args) {
 
 }  // namespace
 
-constexpr int kGemvMaxRows = 32;
+// every row count below the tensor-core threshold (hop of 40 / 64 / 100 rows: 0.65 / 0.66 / 0.69 -> 0.38 / 0.44 / 0.52 ms;
+// the tiled kernel above then only serves BSB_FORCE_FP32 and the K = 0 bias rows)
+constexpr int kGemvMaxRows = kTcMinRows - 1;
 
 cudaError_t launch_gemv_grouped_linear(GroupedArgs& args, cudaStream_t s) {
   int total = 0;
@@ -283,10 +285,11 @@ cudaError_t launch_grouped_linear(GroupedArgs& args, cudaStream_t s) {
   for (int i = 0; i < args.nprob; ++i)
     if (args.p[i].K > 0 && (args.p[i].M < kTcMinRows || args.p[i].Wh == nullptr)) tc = false;
   if (!tc) {
-    static const bool no_gemv = getenv("BSB_NO_GEMV") != nullptr;      // A/B switch
+    static const bool no_gemv = getenv("BSB_NO_GEMV") != nullptr;      // A/B switches
+    static const int gemv_max = getenv("BSB_GEMV_MAX") ? atoi(getenv("BSB_GEMV_MAX")) : kGemvMaxRows;
     bool gemv = args.nprob > 0 && !no_gemv;
     for (int i = 0; i < args.nprob; ++i)
-      if (args.p[i].M > kGemvMaxRows || args.p[i].K > GV_KMAX || args.p[i].O == nullptr || (args.p[i].K > 0 && args.p[i].A == nullptr)) gemv = false;
+      if (args.p[i].M > gemv_max || args.p[i].K > GV_KMAX || args.p[i].O == nullptr || (args.p[i].K > 0 && args.p[i].A == nullptr)) gemv = false;
     return gemv ? launch_gemv_grouped_linear(args, s) : launch_ffma_grouped_linear(args, s);
   }
   cudaError_t e = launch_tc_grouped_linear(args, s);

@@ -158,7 +158,7 @@ def test_forward_recurrent_vs_golden(dev, model, golden_dir):
         s = s2
 
 
-# (C*T <= 32 frame-rows: the small-M Linear kernel, incl. its 8-row chunk edges 8|9, 16, 31|32|33)
+# (C*T < 128 frame-rows: the small-M Linear kernel, incl. its 8-row chunk edges 8|9, 16, 31|32|33)
 @pytest.mark.parametrize("C,T", [(1, 1), (2, 3), (1, 8), (3, 3), (2, 8), (1, 31), (4, 8), (11, 3), (5, 130), (3, 257)])
 def test_forward_ragged_shapes_vs_oracle(dev, model, oracle_sd, C, T):
     rs = np.random.RandomState(100 * C + T)
@@ -180,8 +180,8 @@ def test_recurrent_equals_offline_and_rows_independent(dev, model):
     # offline runs its >=128-row GEMMs on the tensor cores (split-bf16), the hop-by-hop path in fp32
     assert rel(torch.stack(ys, 2), y) < 1e-4
     # rows are independent, bit for bit, wherever the same kernels are selected: 40 and 120 frame-rows both take the
-    # tiled fp32 Linear kernel (33..127 rows; their 480 / 1,440 LSTM rows the tensor-core one), 1 and 2 frame-rows
-    # (12 / 24 LSTM rows) both the small-M one (<= 32 rows)
+    # small-M fp32 Linear kernel (< 128 rows; their 480 / 1,440 LSTM rows the tensor-core one), and so do 1 and 2
+    # frame-rows with their 12 / 24 LSTM rows
     assert torch.equal(model.forward(x[1:2]), y[1:2])
     xs = x[:2, :, :1].contiguous()
     assert torch.equal(model.forward(xs[1:2]), model.forward(xs)[1:2])
