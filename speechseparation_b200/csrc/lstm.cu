@@ -17,7 +17,19 @@
 namespace bsb {
 namespace {
 
-__device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
+// same activation arithmetic as the tensor-core recurrences (lstm_tc.cu, lstm_seq2.cu): ex2.approx + rcp.approx, <= 2 ulp each
+__device__ __forceinline__ float ex2_(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float sigmoidf_(float x) { return rcp_(1.0f + ex2_(-1.4426950408889634f * x)); }
+__device__ __forceinline__ float tanhf_(float x) { return 2.0f * rcp_(1.0f + ex2_(-2.8853900817779268f * x)) - 1.0f; }
 
 __device__ __forceinline__ float sel4(float a, float b, float c, float d, int idx) {
   const float lo = (idx & 1) ? b : a;
@@ -125,8 +137,8 @@ lstm_rec_kernel(const LstmArgs a) {
       const float gf = sel4(recv[0], recv[1], recv[2], recv[3], g ^ 1);
       const float gg = sel4(recv[0], recv[1], recv[2], recv[3], g ^ 2);
       const float go = sel4(recv[0], recv[1], recv[2], recv[3], g ^ 3);
-      const float cn = sigmoidf_(gf) * c[q] + sigmoidf_(gi) * tanhf(gg);
-      const float hn = sigmoidf_(go) * tanhf(cn);
+      const float cn = sigmoidf_(gf) * c[q] + sigmoidf_(gi) * tanhf_(gg);
+      const float hn = sigmoidf_(go) * tanhf_(cn);
       c[q] = cn;
       const int s = 4 * q + g;
       const int sq = seq0 + s;
