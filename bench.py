@@ -208,6 +208,40 @@ def streaming_latency(model, dev, hops: int = 400, rows: int = 2):
             "hop_budget_ms": 1e3 * 1024 / SR, "realtime_factor_p99": (1e3 * 1024 / SR) / q(host, 0.99)}
 
 
+def plugin_latency(model, hops: int = 400):
+    """The LADSPA-shaped C++ host (csrc/plugin.cpp; reference speech-ladspa-onnx.cpp:152-267) driven the way an
+    audio host drives it: run(1024) per hop on HOST buffers; each call copies the block in, replays the hop graph,
+    copies the block out and synchronises. `hop_ms`: the host's own clock around a hop (plugin counters),
+    `run_ms`: wall clock of run() seen by the caller."""
+    import numpy as np
+    from speechseparation_b200.plugin import SpeechSeparatorPlugin, PORT_CONTROL, PORT_IN_L, PORT_IN_R, PORT_OUT_L, PORT_OUT_R
+    plug = SpeechSeparatorPlugin({k: v.detach().cpu() for k, v in model.state_dict().items()}, device=torch.cuda.current_device())
+    rs = np.random.RandomState(11)
+    x = (0.1 * rs.standard_normal((hops + 8) * 1024)).astype(np.float32)
+    y = np.zeros(1024, dtype=np.float32)
+    ctl = np.array([1.0], dtype=np.float32)
+    plug.connect_port(PORT_CONTROL, ctl)
+    plug.connect_port(PORT_OUT_L, y)
+    plug.connect_port(PORT_OUT_R, y)
+    wall, hop = [], []
+    for i in range(hops + 8):
+        blk = x[i * 1024:(i + 1) * 1024]
+        plug.connect_port(PORT_IN_L, blk)
+        plug.connect_port(PORT_IN_R, blk)
+        t0 = time.perf_counter()
+        plug.run(1024)
+        if i >= 8:                                       # first hops: eager warm-up + graph capture
+            wall.append(1e3 * (time.perf_counter() - t0))
+            hop.append(plug.last_hop_ms)
+    plug.close()
+    wall.sort()
+    hop.sort()
+    q = lambda v, p: v[min(len(v) - 1, int(p * len(v)))]
+    return {"config": f"ladspa_descriptor host, run(1024) x {hops} on host buffers, 2 model rows",
+            "hop_ms_p50": q(hop, 0.5), "hop_ms_p99": q(hop, 0.99), "run_ms_p50": q(wall, 0.5), "run_ms_p99": q(wall, 0.99),
+            "hop_budget_ms": 1e3 * 1024 / SR}
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference's own CPU implementation of the path (stock PyTorch ops,
     restated in oracle/) on all host cores; each step is a bounded sample of the workload."""
@@ -438,6 +472,7 @@ def main():
     }
     if world == 1 and not args.no_streaming:
         res["streaming"] = streaming_latency(model, dev, hops=args.stream_hops)
+        res["streaming"]["ladspa_host"] = plugin_latency(model, hops=args.stream_hops)
         # BASELINE.json configs[3]: 512 concurrent sessions (1,024 rows) advanced hop-synchronously; on G GPUs every
         # GPU holds 1024/G rows (sessions are independent, shard.py), so the per-GPU shapes are these row counts
         sess = {}
