@@ -158,8 +158,10 @@ def test_forward_recurrent_vs_golden(dev, model, golden_dir):
         s = s2
 
 
-# (C*T < 128 frame-rows: the small-M Linear kernel, incl. its 8-row chunk edges 8|9, 16, 31|32|33)
-@pytest.mark.parametrize("C,T", [(1, 1), (2, 3), (1, 8), (3, 3), (2, 8), (1, 31), (4, 8), (11, 3), (5, 130), (3, 257)])
+# (C*T < 128 frame-rows: the small-M Linear kernel, incl. its 8-row chunk edges 8|9, 16, 31|32|33 and the
+# hand-over to the tensor-core Linears at 127|128|129)
+@pytest.mark.parametrize("C,T", [(1, 1), (2, 3), (1, 8), (3, 3), (2, 8), (1, 31), (4, 8), (11, 3), (1, 127), (1, 128), (1, 129),
+                                 (5, 130), (3, 257)])
 def test_forward_ragged_shapes_vs_oracle(dev, model, oracle_sd, C, T):
     rs = np.random.RandomState(100 * C + T)
     x = torch.from_numpy((rs.standard_normal((C, 2050, T)) * 2.0).astype(np.float32))
