@@ -472,7 +472,10 @@ def main():
     }
     if world == 1 and not args.no_streaming:
         res["streaming"] = streaming_latency(model, dev, hops=args.stream_hops)
-        res["streaming"]["ladspa_host"] = plugin_latency(model, hops=args.stream_hops)
+        try:
+            res["streaming"]["ladspa_host"] = plugin_latency(model, hops=args.stream_hops)
+        except Exception as e:                     # a secondary figure must not cost the bench line
+            res["streaming"]["ladspa_host"] = {"error": f"{type(e).__name__}: {e}"}
         # BASELINE.json configs[3]: 512 concurrent sessions (1,024 rows) advanced hop-synchronously; on G GPUs every
         # GPU holds 1024/G rows (sessions are independent, shard.py), so the per-GPU shapes are these row counts
         sess = {}
