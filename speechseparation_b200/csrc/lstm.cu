@@ -37,7 +37,9 @@ __device__ __forceinline__ float sel4(float a, float b, float c, float d, int id
   return (idx & 2) ? hi : lo;
 }
 
-template <int S>
+// NV: sequences of the group that exist (compile time, so the mat-vec of the empty slots disappears): S, or 1 / 2
+// for the single short group of a 1- or 2-row streaming hop (band axis: one sequence per row).
+template <int S, int NV>
 __global__ void __launch_bounds__(256)
 lstm_rec_kernel(const LstmArgs a) {
   static_assert(S % 4 == 0, "S must be a multiple of 4");
@@ -114,7 +116,7 @@ lstm_rec_kernel(const LstmArgs a) {
 #pragma unroll
     for (int k4 = 0; k4 < kFeat / 4; ++k4) {
 #pragma unroll
-      for (int s = 0; s < S; ++s) {
+      for (int s = 0; s < NV; ++s) {
         const float4 hv = *reinterpret_cast<const float4*>(&hs[cur][s][4 * k4]);
         acc[s] = fmaf(w[4 * k4 + 0], hv.x, acc[s]);
         acc[s] = fmaf(w[4 * k4 + 1], hv.y, acc[s]);
@@ -164,14 +166,18 @@ cudaError_t launch_lstm(const LstmArgs& a, cudaStream_t s) {
   if (a.nseq <= 0 || a.nsteps <= 0) return cudaSuccess;
   // few long sequences (time axis): small S spreads them over the SMs;
   // many short sequences (band axis): larger S amortises the W_hh register load.
-  if (a.nseq <= 4 * 148 * 2) {
+  if (a.nseq <= 2) {                             // 1- or 2-row hop, band axis
+    dim3 grid(1, a.ndir);
+    if (a.nseq == 1) lstm_rec_kernel<4, 1><<<grid, 256, 0, s>>>(a);
+    else lstm_rec_kernel<4, 2><<<grid, 256, 0, s>>>(a);
+  } else if (a.nseq <= 4 * 148 * 2) {
     constexpr int S = 4;
     dim3 grid((a.nseq + S - 1) / S, a.ndir);
-    lstm_rec_kernel<S><<<grid, 256, 0, s>>>(a);
+    lstm_rec_kernel<S, S><<<grid, 256, 0, s>>>(a);
   } else {
     constexpr int S = 8;
     dim3 grid((a.nseq + S - 1) / S, a.ndir);
-    lstm_rec_kernel<S><<<grid, 256, 0, s>>>(a);
+    lstm_rec_kernel<S, S><<<grid, 256, 0, s>>>(a);
   }
   count_launch();
   return cudaGetLastError();
