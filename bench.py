@@ -297,6 +297,8 @@ def main():
     from speechseparation_b200 import BSRNN, _lib, aggregate_throughput
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
+    from speechseparation_b200.shard import bind_to_gpu_numa_node
+    numa_node = bind_to_gpu_numa_node(dev.index if dev.index is not None else 0) if world > 1 else -1
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     l = _lib.lib()
@@ -464,7 +466,7 @@ def main():
                    "weights": "random init, torch.manual_seed(0)"},
         "e2e": {"value": units_e / tmax_e, "unit": "audio-sec/s", "h2d_bytes_per_step": host_in.numel() * 4,
                 "d2h_bytes_per_step": host_out.numel() * 4, "ms_per_step": 1e3 * tmax_e / args.steps,
-                "api": "speechseparation_b200.BatchSeparator.submit (H2D | kernels | D2H on three streams, 2 buffer pairs)",
+                "host_numa_node_rank0": numa_node, "api": "speechseparation_b200.BatchSeparator.submit (H2D | kernels | D2H on three streams, 2 buffer pairs)",
                 "serial_value": units_s / tmax_s, "serial_ms_per_step": 1e3 * tmax_s / args.steps,
                 "max_abs_diff_vs_resident": e2e_check},
         "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "kernels": kernels,

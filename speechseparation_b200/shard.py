@@ -35,3 +35,28 @@ def aggregate_throughput(local_units: float, local_seconds: float, device=None) 
     dist.all_reduce(u, op=dist.ReduceOp.SUM)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(u.item()), float(t.item())
+
+
+def bind_to_gpu_numa_node(device_index: int) -> int:
+    """Pin this process to the CPUs of the NUMA node its GPU hangs off, BEFORE any pinned host buffer is allocated
+    (pages are placed on the node of the allocating thread). With one process per GPU and host buffers of 113 MB per
+    direction and step, copies that cross the socket interconnect are what keeps the host-buffer path from scaling.
+    Returns the node, or -1 when the topology is not exposed (then nothing is changed)."""
+    import os
+    try:
+        p = torch.cuda.get_device_properties(device_index)
+        bdf = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read().strip())
+        if node < 0:
+            return -1
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return -1
+        os.sched_setaffinity(0, cpus)
+        return node
+    except (OSError, ValueError, AttributeError):
+        return -1
