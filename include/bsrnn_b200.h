@@ -12,7 +12,11 @@
  *     nothing here allocates device memory, scratch space is a caller-provided workspace
  *     sized by bsb_workspace_bytes();
  *   - `stream` is a cudaStream_t passed as void* (0 = default stream); work is only
- *     enqueued, never synchronised (except bsb_stage_times);
+ *     enqueued, never synchronised (except bsb_stage_times and bsb_init);
+ *   - thread-compatible: host threads may call concurrently with different workspaces / streams (no per-call state
+ *     lives in process globals; the stage-timing marks are per host thread); one workspace serves one stream at a time;
+ *   - multi-device: every call acts on the CURRENT device (cudaSetDevice) of the calling thread; one process may
+ *     use several devices in turn;
  *   - "rows" C = dim 0 of the reference tensors (channels x clips x sessions),
  *     T = frames, frame-row = one frame of one row.
  *
@@ -49,6 +53,11 @@ extern "C" {
 
 /* --- introspection ------------------------------------------------------------------ */
 int         bsb_version(void);
+/* One-time set-up of `device` (-1 = the current one): uploads the periodic-Hann window and FFT twiddle tables
+ * (28 KB, the library's only device allocation). Call it once per device before the first signal-wrap call so
+ * that no launch call allocates or synchronises (the Python host does so in BSRNN.packed_weights and the plugin in
+ * its constructor); a launch on a device that was never initialised creates the tables lazily. Thread-safe. */
+int         bsb_init(int device);
 const char* bsb_error_string(int code);
 /* band widths in bins [1,2,3,6,12,24,48,96,192,384,257,0] -- replaces generate_bandsplits()
  * (bsrnn.py:247-326), which the reference re-evaluates on every forward. */

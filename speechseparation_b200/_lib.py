@@ -20,6 +20,7 @@ vp, ci, cll, csz, cfp = C.c_void_p, C.c_int, C.c_longlong, C.c_size_t, C.c_void_
 # name -> (restype, argtypes); mirrors include/bsrnn_b200.h one to one
 SIGNATURES = {
     "bsb_version": (ci, []),
+    "bsb_init": (ci, [ci]),
     "bsb_error_string": (C.c_char_p, [ci]),
     "bsb_band_widths": (ci, [C.POINTER(ci)]),
     "bsb_tensor_numel": (cll, [ci]),

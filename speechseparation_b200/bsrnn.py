@@ -120,27 +120,55 @@ class BSRNN(nn.Module):
         self.bandFCs_back_post = nn.ModuleList([
             (nn.Sequential(nn.Linear(x * 2, x * 2), lrelu(), nn.Linear(x * 2, x * 2))
              if x > 0 else nn.Sequential(TrainableConstantModule([0]))) for x in band_split[0]])
+        self._reset_caches()
+
+    def _reset_caches(self):
         self._packed: Optional[torch.Tensor] = None
         self._packed_sig = None
-        self._ws: Optional[torch.Tensor] = None
+        self._packed_event = None         # recorded after bsb_pack_weights on the packing stream
+        self._packed_stream = None
+        self._plist = None                # cached list(self.parameters()): the module walk costs ~0.4 ms per call
+        self._ws = {}                     # workspace per (device, stream): one workspace serves one stream at a time
 
     # ---- pickling: device caches are not part of the module's state (infer-streaming.py:49) ----
     def __getstate__(self):
         d = self.__dict__.copy()
-        d["_packed"] = None
-        d["_packed_sig"] = None
-        d["_ws"] = None
+        for k in ("_packed", "_packed_sig", "_packed_event", "_packed_stream", "_plist"):
+            d[k] = None
+        d["_ws"] = {}
         return d
+
+    def __setstate__(self, d):
+        super().__setstate__(d)
+        self._reset_caches()
+
+    def _apply(self, fn, *a, **kw):       # .to() / .cuda() / .float(): parameter storage is replaced
+        self.invalidate_packed()
+        return super()._apply(fn, *a, **kw)
+
+    def invalidate_packed(self):
+        """Drop the packed-weight cache. In-place updates (optimizer steps, load_state_dict, p.data.copy_) and
+        .to() are tracked automatically; call this after REPLACING a Parameter object of a sub-module."""
+        self._packed = self._packed_sig = self._packed_event = self._packed_stream = self._plist = None
 
     # ---- weight packing ---------------------------------------------------------------------
     def _signature(self):
-        return tuple((p.data_ptr(), p._version) for p in self.parameters())
+        # tensor versions only increase, so their sum changes with every in-place update of any parameter;
+        # the data pointers catch storage replacement (.data = ..., .to())
+        pl = self._plist
+        if pl is None:
+            pl = self._plist = list(self.parameters())
+        return (sum(p._version for p in pl), tuple(p.data_ptr() for p in pl))
 
     def packed_weights(self, device: torch.device) -> torch.Tensor:
         """Packed device copy of the 288 parameters; re-packed whenever a parameter's storage
-        or version changes (load_state_dict, .to(), optimizer steps)."""
+        or version changes (load_state_dict, .to(), optimizer steps). The buffer is produced on the stream
+        that is current at packing time; any other stream that asks for it is made to wait for that work."""
         sig = self._signature()
         if self._packed is not None and self._packed_sig == sig and self._packed.device == device:
+            cur = torch.cuda.current_stream(device)
+            if cur != self._packed_stream:
+                cur.wait_event(self._packed_event)
             return self._packed
         params = list(self.state_dict(keep_vars=True).values())
         l = _lib.lib()
@@ -156,16 +184,27 @@ class BSRNN(nn.Module):
         keep = [p.detach().contiguous() for p in params]
         table = (ctypes.c_void_p * 288)(*[(t.data_ptr() if t.numel() else None) for t in keep])
         with torch.cuda.device(device):
+            _lib.check(l.bsb_init(device.index if device.index is not None else -1), "bsb_init")
             packed = torch.empty(l.bsb_packed_weights_bytes() // 4, dtype=torch.float32, device=device)
             _lib.check(l.bsb_pack_weights(table, 288, packed.data_ptr(), _stream_ptr()), "bsb_pack_weights")
-        self._packed, self._packed_sig = packed, sig
+            ev = torch.cuda.Event()
+            ev.record()
+            self._packed_stream = torch.cuda.current_stream(device)
+        packed._bsb_keep = keep           # contiguous copies of non-contiguous parameters must outlive the packing kernels
+        self._packed, self._packed_sig, self._packed_event = packed, sig, ev
         return packed
 
     def workspace(self, nbytes: int, device: torch.device) -> torch.Tensor:
-        if self._ws is None or self._ws.device != device or self._ws.numel() < nbytes:
-            self._ws = None
-            self._ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
-        return self._ws
+        """Scratch buffer of the CURRENT stream on `device` (grown on demand). Two streams never share one: a
+        workspace serves one stream at a time (include/bsrnn_b200.h)."""
+        key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+        ws = self._ws.get(key)
+        if ws is None or ws.numel() < nbytes:
+            if ws is not None:
+                ws.record_stream(torch.cuda.current_stream(device))     # queued work may still use the old block
+            self._ws[key] = None
+            ws = self._ws[key] = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        return ws
 
     # ---- checks ------------------------------------------------------------------------------
     @staticmethod

@@ -1,5 +1,6 @@
 // C ABI of libbsrnn_b200.so (include/bsrnn_b200.h): argument checks, workspace carving and the
 // stage-by-stage orchestration of the kernels in linear.cu / lstm.cu / fft.cu.
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -26,12 +27,14 @@ inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 // ---- stage timing -----------------------------------------------------------------------
+// (measurement aid: the switch is process-wide, the marks belong to the calling host thread, so two threads driving
+// two streams do not overwrite each other's events; bsb_stage_times reads the calling thread's marks)
 constexpr int kMaxMarks = 96;
-bool g_timing = false;
-int g_nmarks = 0;
-cudaEvent_t g_ev[kMaxMarks];
-bool g_ev_made[kMaxMarks] = {};
-char g_names[kMaxMarks][40];
+std::atomic<bool> g_timing{false};
+thread_local int g_nmarks = 0;
+thread_local cudaEvent_t g_ev[kMaxMarks];
+thread_local bool g_ev_made[kMaxMarks] = {};
+thread_local char g_names[kMaxMarks][40];
 
 void marks_reset() { if (g_timing) g_nmarks = 0; }
 // record the END of stage `name` (the first mark of a call is named "begin")
@@ -173,7 +176,16 @@ int single_linear(const void* packed, const Lin& l, const float* A, int lda, flo
 // =========================================================================================
 extern "C" {
 
-int bsb_version(void) { return 100; }
+int bsb_version(void) { return 200; }
+
+int bsb_init(int device) {
+  int prev = 0;
+  CK(cudaGetDevice(&prev));
+  if (device >= 0 && device != prev) CK(cudaSetDevice(device));
+  const cudaError_t e = init_signal_tables();
+  if (device >= 0 && device != prev) cudaSetDevice(prev);
+  return (int)e;
+}
 
 const char* bsb_error_string(int code) {
   switch (code) {
@@ -267,7 +279,7 @@ size_t bsb_stream_workspace_bytes(int C) {
 
 int bsb_num_frames(long long L) { return L <= BSB_HOP ? -1 : (int)(1 + L / BSB_HOP); }
 
-int bsb_set_stage_timing(int enabled) { g_timing = enabled != 0; g_nmarks = 0; return 0; }
+int bsb_set_stage_timing(int enabled) { g_timing.store(enabled != 0); g_nmarks = 0; return 0; }
 int bsb_stage_count(void) { return g_nmarks > 0 ? g_nmarks - 1 : 0; }
 const char* bsb_stage_name(int i) { return (i >= 0 && i + 1 < g_nmarks) ? g_names[i + 1] : ""; }
 int bsb_stage_times(float* ms, int n) {
@@ -284,7 +296,7 @@ int bsb_stage_times(float* ms, int n) {
   }
   return cnt;
 }
-long long bsb_launch_count(void) { return g_launches; }
+long long bsb_launch_count(void) { return g_launches.load(); }
 int bsb_set_force_fp32(int on) { set_force_ffma(on); return 0; }
 
 }  // extern "C"
@@ -386,6 +398,7 @@ int run_rnn_block(int j, const float* fin, int C, int T, const void* packed, con
   if (!band && T >= kLstmSeqMinSteps && !force_ffma()) {
     // latency path: both layers in one launch, fc_in and W_ih fused into the recurrence (lstm_seq2.cu)
     float* hl[2] = {w.hbuf, w.xproj};
+    int fused = 0;
     {
       LstmSeq2Args a{};
       a.x = fin; a.hmid = hl[0]; a.hout = hl[1];
@@ -401,11 +414,11 @@ int run_rnn_block(int j, const float* fin, int C, int T, const void* packed, con
       if (rows >= kTcMinRows) { a.hplanes = w.planeA; a.hp_lo = kPlaneBlock; }
       a.flags = reinterpret_cast<int*>(w.t64);                // t64 is only used by the FFMA fallback path
       a.fcw = PW(packed, R.fc.w); a.ldfcw = R.fc.Kpad; a.fcb = PW(packed, R.fc.b); a.fc_out = fout;
-      CK(launch_lstm_seq2(a, s));
+      CK(launch_lstm_seq2(a, s, &fused));
       std::snprintf(nm, sizeof(nm), "rnn%d.rec", j);
       mark(nm, s);
     }
-    if (lstm_seq2_fused_fc()) return 0;                        // the launch carried fc + residual (third CTA per group)
+    if (fused) return 0;                        // the launch carried fc + residual (third CTA per group)
     if (rows >= kTcMinRows)
       CKI(single_linear(packed, R.fc, hl[1], ldh, fout, kFeat, rows, ACT_NONE, fin, kFeat, s, w.planeA, kPlaneBlock));
     else

@@ -501,6 +501,10 @@ cudaError_t ensure_tables(Tables** out) {
 
 }  // namespace
 
+cudaError_t init_signal_tables() {
+  Tables* t = nullptr;
+  return ensure_tables(&t);
+}
 const float* builtin_window(cudaStream_t, cudaError_t* err) {
   Tables* t = nullptr;
   *err = ensure_tables(&t);
@@ -548,14 +552,9 @@ cudaError_t launch_istft_frames(const float* xf, int xs, int C, int T, const flo
   const int grid = (nwork + kFrameWarps - 1) / kFrameWarps;
   if (staged) {
     constexpr int smem = kFrameWarps * kIstftWarpSmem;
-    static bool attr_set[64] = {};
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-      cudaError_t e = cudaFuncSetAttribute(istft_warp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-      if (e != cudaSuccess) return e;
-      attr_set[dev] = true;
-    }
+    static SmemOptIn opt;
+    const cudaError_t e = opt_in_smem(istft_warp_kernel<true>, smem, opt);
+    if (e != cudaSuccess) return e;
     istft_warp_kernel<true><<<grid, kFrameWarps * 32, smem, s>>>(xf, xs, T, nseg, nwork, window, tw, wav, per);
   } else {
     istft_warp_kernel<false><<<grid, kFrameWarps * 32, kFrameWarps * 32 * kTr * 8, s>>>(xf, xs, T, nseg, nwork, window, tw, wav, per);

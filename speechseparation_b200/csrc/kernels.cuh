@@ -1,14 +1,35 @@
 // Internal kernel-launch interface shared by the .cu files of libbsrnn_b200.so.
 #pragma once
 #include <cuda_runtime.h>
+#include <atomic>
 #include <cstdint>
 #include "layout.h"
 
 namespace bsb {
 
-// every kernel launch goes through this counter (bsb_launch_count)
-extern long long g_launches;
-inline void count_launch(int n = 1) { g_launches += n; }
+// every kernel launch goes through this counter (bsb_launch_count); host threads may launch concurrently
+extern std::atomic<long long> g_launches;
+inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) applies to the CURRENT device only: one flag per (kernel, device).
+// `*dev_out` receives the current device. Racing first calls both set the attribute, which is harmless.
+struct SmemOptIn { std::atomic<bool> done[64]; };
+template <class K>
+inline cudaError_t opt_in_smem(K kernel, int bytes, SmemOptIn& st, int* dev_out = nullptr) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev_out) *dev_out = dev;
+  if (dev < 0 || dev >= 64) return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (!st.done[dev].load(std::memory_order_acquire)) {
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) return e;
+    st.done[dev].store(true, std::memory_order_release);
+  }
+  return cudaSuccess;
+}
+// SM count of a device, cached
+int sm_count(int dev);
 
 // ------------------------------------------------------------------------------------
 // grouped Linear:  O[m][n] = epi( sum_k A[m][k] * W[n][k] + bias[n] )
@@ -129,8 +150,8 @@ struct LstmSeq2Args {
   int exp;                   // timing-experiment switches (BSB_SEQ2_EXP: 1 no cell update, 2 no recurrent MMAs, 8 no x loads,
                              // 16 no h flush), 0 in production
 };
-cudaError_t launch_lstm_seq2(const LstmSeq2Args& a, cudaStream_t s);
-bool lstm_seq2_fused_fc();     // did the most recent launch_lstm_seq2 include the output Linear?
+// *fused (optional) = 1 when the launch carried the block's output Linear + residual (third CTA per group)
+cudaError_t launch_lstm_seq2(const LstmSeq2Args& a, cudaStream_t s, int* fused = nullptr);
 constexpr int kLstmSeqMinSteps = 2;  // single steps (streaming hops) stay on the FFMA recurrence
 // Band-axis blocks below this many sequences (frame-rows) run as GEMM projections + the FFMA recurrence: the tcgen05
 // layer kernel puts 128 sequences on one CTA for ~66-80 us whatever the count, so 128 rows = 2 CTAs on 148 SMs.
@@ -159,6 +180,9 @@ cudaError_t launch_to_frames(const float* x, int C, int T, float* xf, int xs, cu
 cudaError_t launch_from_frames(const float* xf, int xs, int C, int T, float* x, cudaStream_t s);
 const float* builtin_window(cudaStream_t s, cudaError_t* err);   // device float[2048], periodic Hann
 const float2* twiddle_tables(cudaStream_t s, cudaError_t* err);  // device: [1024] W_1024^k then [1025] W_2048^k
+// creates the window / twiddle tables of the CURRENT device (the library's only device allocation: 28 KB, once per
+// device). bsb_init() calls it so that no launch call allocates; a launch on a device never initialised creates them lazily.
+cudaError_t init_signal_tables();
 
 // ------------------------------------------------------------------------------------
 // evaluation sums (m_dataset.py:202-226): stats[rows][5] = sum|e-r|, sum r^2, sum (e-r)^2, sum e r, sum e^2

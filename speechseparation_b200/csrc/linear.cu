@@ -13,7 +13,18 @@
 
 namespace bsb {
 
-long long g_launches = 0;
+std::atomic<long long> g_launches{0};
+
+int sm_count(int dev) {
+  static std::atomic<int> cache[64];
+  if (dev < 0 || dev >= 64) return 148;
+  int v = cache[dev].load(std::memory_order_relaxed);
+  if (v <= 0) {
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) return 148;
+    cache[dev].store(v, std::memory_order_relaxed);
+  }
+  return v;
+}
 
 namespace {
 
@@ -277,12 +288,12 @@ cudaError_t launch_ffma_grouped_linear(GroupedArgs& args, cudaStream_t s) {
   return cudaGetLastError();
 }
 
-static int g_force_ffma = 0;
-void set_force_ffma(int on) { g_force_ffma = on; }
-int force_ffma() { return g_force_ffma; }
+static std::atomic<int> g_force_ffma{0};
+void set_force_ffma(int on) { g_force_ffma.store(on); }
+int force_ffma() { return g_force_ffma.load(std::memory_order_relaxed); }
 
 cudaError_t launch_grouped_linear(GroupedArgs& args, cudaStream_t s) {
-  bool tc = !g_force_ffma && args.nprob > 0;
+  bool tc = !force_ffma() && args.nprob > 0;
   for (int i = 0; i < args.nprob; ++i)
     if (args.p[i].K > 0 && (args.p[i].M < kTcMinRows || args.p[i].Wh == nullptr)) tc = false;
   if (!tc) {

@@ -596,23 +596,19 @@ extern "C" int bsb_debug_seq2_trace(long long* host, int n) {
 }
 #endif
 
-static int g_last_fused = 0;
-bool lstm_seq2_fused_fc() { return g_last_fused != 0; }
-
-cudaError_t launch_lstm_seq2(const LstmSeq2Args& a, cudaStream_t s) {
+cudaError_t launch_lstm_seq2(const LstmSeq2Args& a, cudaStream_t s, int* fused) {
+  if (fused) *fused = 0;
   if (a.nseq <= 0 || a.nsteps <= 0) return cudaSuccess;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(lstm_seq2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
-    if (e != cudaSuccess) return e;
-    attr_set = true;
-  }
-  int dev = 0, sms = 148;
-  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  static SmemOptIn opt;
+  int dev = 0;
+  cudaError_t e = opt_in_smem(lstm_seq2_kernel, SMEM_BYTES, opt, &dev);
+  if (e != cudaSuccess) return e;
+  const int sms = sm_count(dev);
   // 8 sequences per CTA halve the cell update of a step (one fragment per lane instead of two); taken when all
   // CTAs are still co-resident, i.e. for short batches and long-form clips (cfg 1, 3, 5)
   const int g8 = (a.nseq + TS - 1) / TS, g16 = (a.nseq + SQ - 1) / SQ;
-  const bool can_fuse = a.fcw != nullptr && a.fc_out != nullptr && a.fc_out != a.x && !(std::getenv("BSB_SEQ2_NOFC"));
+  static const bool no_fc = std::getenv("BSB_SEQ2_NOFC") != nullptr;      // A/B switch, read once
+  const bool can_fuse = a.fcw != nullptr && a.fc_out != nullptr && a.fc_out != a.x && !no_fc;
   // preference: fused output Linear (third CTA per group) as long as all CTAs are co-resident, small groups first
   int group = SQ, fuse = 0;
   if (can_fuse && 3 * g8 <= sms) { group = TS; fuse = 1; }
@@ -625,10 +621,10 @@ cudaError_t launch_lstm_seq2(const LstmSeq2Args& a, cudaStream_t s) {
   b.group = group;
   b.fuse_fc = fuse;
   b.ngroups = groups;
-  cudaError_t e = cudaMemsetAsync(a.flags, 0, sizeof(int) * 2 * groups, s);
+  e = cudaMemsetAsync(a.flags, 0, sizeof(int) * 2 * groups, s);
   if (e != cudaSuccess) return e;
   lstm_seq2_kernel<<<(fuse ? 3 : 2) * groups, THREADS, SMEM_BYTES, s>>>(b);
-  g_last_fused = fuse;
+  if (fused) *fused = fuse;
   count_launch();
   return cudaGetLastError();
 }

@@ -270,13 +270,9 @@ lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
 
 template <int KIN>
 cudaError_t launch_kin(const LstmTcArgs& a, cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(lstm_tc_kernel<KIN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         Cfg<KIN>::SMEM);
-    if (e != cudaSuccess) return e;
-    attr_set = true;
-  }
+  static SmemOptIn opt;
+  cudaError_t e = opt_in_smem(lstm_tc_kernel<KIN>, Cfg<KIN>::SMEM, opt);
+  if (e != cudaSuccess) return e;
   dim3 grid((a.nseq + TILE - 1) / TILE, a.ndir);
   lstm_tc_kernel<KIN><<<grid, THREADS, Cfg<KIN>::SMEM, s>>>(a);
   count_launch();

@@ -129,6 +129,7 @@ struct bsb_plugin {
     if (!weights || n_floats != weight_floats() || dev < 0) return BSB_E_ARG;
     device = dev;
     PCK(cudaSetDevice(device));
+    PCI(bsb_init(device));           // window / twiddle tables: nothing allocates on the audio thread later
     PCK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     // flat image -> 288 device pointers -> packed buffer
     float* d_flat = nullptr;

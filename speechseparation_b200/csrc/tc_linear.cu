@@ -592,7 +592,6 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
   }
 }
 
-int g_sm_count[64] = {};
 // Plane-operand launches on CTA pairs (cta_group::2, 256-row tiles, each CTA loads half of the W rows) are verified
 // bit-identical to the single-CTA path but measured slower on this workload (5.2 vs 4.5 ms/step, profiles/
 // r01_summary.md): opt-in for experiments.
@@ -603,24 +602,13 @@ const bool g_pair = getenv("BSB_PAIR") != nullptr;
 // Launch the problems of `args` that have K > 0 on the tensor-core kernel. Problems are taken
 // in descending-K order so that the static round-robin schedule ends with the cheap tiles.
 cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(tc_grouped_linear_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<false>());
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(tc_grouped_linear_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<false>());
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(tc_grouped_linear_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<true>());
-    if (e != cudaSuccess) return e;
-    attr_set = true;
-  }
+  static SmemOptIn opt[3];
   int dev = 0;
-  cudaError_t e = cudaGetDevice(&dev);
+  cudaError_t e = opt_in_smem(tc_grouped_linear_kernel<false, false>, smem_bytes<false>(), opt[0], &dev);
   if (e != cudaSuccess) return e;
-  if (dev >= 0 && dev < 64 && g_sm_count[dev] == 0) {
-    e = cudaDeviceGetAttribute(&g_sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
-    if (e != cudaSuccess) return e;
-  }
-  const int sms = (dev >= 0 && dev < 64) ? g_sm_count[dev] : 148;
+  if ((e = opt_in_smem(tc_grouped_linear_kernel<true, false>, smem_bytes<false>(), opt[1])) != cudaSuccess) return e;
+  if ((e = opt_in_smem(tc_grouped_linear_kernel<true, true>, smem_bytes<true>(), opt[2])) != cudaSuccess) return e;
+  const int sms = sm_count(dev);
 
   int order[kMaxProb], n = 0;
   for (int i = 0; i < args.nprob; ++i)
