@@ -154,6 +154,12 @@ size_t bsb_stream_workspace_bytes(int C);
 int bsb_pair_stats(const float* est, long long est_stride, const float* ref, long long ref_stride,
                    int rows, long long n, double* stats, void* stream);
 
+/* sdr2 of m_dataset.train_infer exactly as the reference reduces it for its [1][C][L] samples (m_dataset.py:219-222,
+ * `dim=1` = the channel axis): out[0] (DEVICE double, zeroed by the call) =
+ *   sum_l 10 log10( (sum_c src[c][l]^2 + 1e-9) / (sum_c (src[c][l] - mix[c][l])^2 + 1e-9) ); sdr2 = out[0] / n. */
+int bsb_channel_sdr(const float* mix, long long mix_stride, const float* src, long long src_stride,
+                    int rows, long long n, double* out, void* stream);
+
 /* --- measurement -----------------------------------------------------------------------------
  * When enabled, the orchestration functions record CUDA events on `stream` between their
  * stages. bsb_stage_times synchronises on the last event and returns per-stage milliseconds

@@ -335,13 +335,13 @@ def forward_recurrent(sd, x: torch.Tensor, state: torch.Tensor):
 # ----------------------------------------------------------------------------------------
 # signal wrap restatement
 # ----------------------------------------------------------------------------------------
-def hann() -> torch.Tensor:
-    return torch.hann_window(N_FFT)                        # periodic, m_dataset.py:187
+def hann(device=None) -> torch.Tensor:
+    return torch.hann_window(N_FFT, device=device)         # periodic, m_dataset.py:187
 
 
 def stft_pack(wav: torch.Tensor) -> torch.Tensor:
     """m_dataset.py:187-190: [C,L] -> [C,2050,T], row 2k = Re bin k, 2k+1 = Im bin k."""
-    s = torch.stft(wav, n_fft=N_FFT, hop_length=HOP, return_complex=True, window=hann())
+    s = torch.stft(wav, n_fft=N_FFT, hop_length=HOP, return_complex=True, window=hann(wav.device))
     s = torch.stack((s.real, s.imag), dim=2)
     return s.reshape(s.shape[0], -1, s.shape[3]).contiguous()
 
@@ -350,7 +350,7 @@ def unpack_istft(x: torch.Tensor) -> torch.Tensor:
     """m_dataset.py:192-195 with x.shape[0] in place of the literal 2: [C,2050,T] -> [C,1024(T-1)]."""
     x = x.reshape(x.shape[0], -1, 2, x.shape[2])
     xc = torch.complex(x[:, :, 0, :].contiguous(), x[:, :, 1, :].contiguous())
-    return torch.istft(xc, n_fft=N_FFT, hop_length=HOP, window=hann())
+    return torch.istft(xc, n_fft=N_FFT, hop_length=HOP, window=hann(x.device))
 
 
 def separate(sd, wav: torch.Tensor) -> torch.Tensor:
@@ -449,7 +449,13 @@ def sdr(est: torch.Tensor, ref: torch.Tensor) -> torch.Tensor:
 def train_infer(sd, waveform: torch.Tensor, speech: torch.Tensor):
     """m_dataset.train_infer with discriminator=None and lossfn=L1Loss(mean) (m_dataset.py:202-226,
     train.py:54,140), `x.shape[0]` in place of the literal 2 of m_dataset.py:192.
-    Returns (loss, sdr, sdr2, sdr3) as python floats (float64 arithmetic for the reductions)."""
+    waveform / speech: [1,C,L] as the reference's DataLoader yields them, or [C,L]. sdr2 sums over `dim=1` of the
+    UN-squeezed sample exactly as m_dataset.py:219-222 does: the channel axis for [1,C,L], time for [C,L].
+    Returns (loss, sdr, sdr2, sdr3) as python floats (float64 arithmetic for the reductions).
+    Pinned by tests/test_oracle_golden.py::test_train_infer_matches_literal_restatement."""
+    sample0, sample1 = waveform, speech
+    if waveform.dim() == 3:
+        waveform, speech = waveform.squeeze(0), speech.squeeze(0)
     spec = stft_pack(waveform)
     x = forward(sd, spec)
     x_time = unpack_istft(x)
@@ -463,8 +469,8 @@ def train_infer(sd, waveform: torch.Tensor, speech: torch.Tensor):
     n2s = sp_time.double().square().sum(1) + 1e-9
     n2d = (x_time.double() - sp_time.double()).square().sum(1) + 1e-9
     sdr_ = (10 * torch.log10(n2s / n2d)).mean()
-    n2s2 = speech.double().square().sum(1) + 1e-9
-    n2d2 = (speech.double() - waveform.double()).square().sum(1) + 1e-9
+    n2s2 = sample1.double().square().sum(1) + 1e-9
+    n2d2 = (sample1.double() - sample0.double()).square().sum(1) + 1e-9
     sdr2 = (10 * torch.log10(n2s2 / n2d2)).mean()
     sdr3 = si_sdr(x_time, sp_time).mean()
     return float(loss), float(sdr_), float(sdr2), float(sdr3)

@@ -45,6 +45,7 @@ SIGNATURES = {
     "bsb_stream_step_mix": (ci, [cfp, ci, cfp, vp, cfp, cfp, cfp, cfp, cfp, cfp, vp, csz, vp]),
     "bsb_stream_workspace_bytes": (csz, [ci]),
     "bsb_pair_stats": (ci, [cfp, cll, cfp, cll, ci, cll, vp, vp]),
+    "bsb_channel_sdr": (ci, [cfp, cll, cfp, cll, ci, cll, vp, vp]),
     "bsb_set_stage_timing": (ci, [ci]),
     "bsb_stage_count": (ci, []),
     "bsb_stage_name": (C.c_char_p, [ci]),

@@ -705,4 +705,12 @@ int bsb_pair_stats(const float* est, long long est_stride, const float* ref, lon
   return 0;
 }
 
+int bsb_channel_sdr(const float* mix, long long mix_stride, const float* src, long long src_stride, int rows,
+                    long long n, double* out, void* stream) {
+  if (!mix || !src || !out || rows <= 0 || n <= 0 || mix_stride < n || src_stride < n) return BSB_E_ARG;
+  if ((reinterpret_cast<uintptr_t>(out) & 7) != 0) return BSB_E_ALIGN;
+  CK(launch_channel_sdr(mix, mix_stride, src, src_stride, rows, n, out, S(stream)));
+  return 0;
+}
+
 }  // extern "C"

@@ -73,4 +73,45 @@ cudaError_t launch_pair_stats(const float* est, long long est_stride, const floa
   return cudaGetLastError();
 }
 
+// sdr2 of m_dataset.train_infer as the reference actually reduces it (m_dataset.py:219-222): `sample` keeps its
+// leading batch-1 dimension there, so `dim=1` of [1][C][L] is the CHANNEL axis: per sample l,
+//   q(l) = 10 log10( (sum_c s[c][l]^2 + 1e-9) / (sum_c (s[c][l] - m[c][l])^2 + 1e-9) ),   sdr2 = mean_l q(l).
+// out[0] (double, zeroed by the launch) = sum_l q(l).
+__global__ void __launch_bounds__(kStatThreads)
+channel_sdr_kernel(const float* __restrict__ mix, long long mix_stride, const float* __restrict__ src,
+                   long long src_stride, int rows, long long n, double* __restrict__ out) {
+  double acc = 0.0;
+  for (long long l = (long long)blockIdx.x * kStatThreads + threadIdx.x; l < n; l += (long long)gridDim.x * kStatThreads) {
+    float ss = 0.f, dd = 0.f;
+    for (int c = 0; c < rows; ++c) {
+      const float sv = __ldg(src + c * src_stride + l), mv = __ldg(mix + c * mix_stride + l);
+      ss = fmaf(sv, sv, ss);
+      dd = fmaf(sv - mv, sv - mv, dd);
+    }
+    acc += 10.0 * (double)log10f((ss + 1e-9f) / (dd + 1e-9f));
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  __shared__ double red[kStatThreads / 32];
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s = 0.0;
+#pragma unroll
+    for (int w = 0; w < kStatThreads / 32; ++w) s += red[w];
+    atomicAdd(out, s);
+  }
+}
+
+cudaError_t launch_channel_sdr(const float* mix, long long mix_stride, const float* src, long long src_stride,
+                               int rows, long long n, double* out, cudaStream_t s) {
+  cudaError_t e = cudaMemsetAsync(out, 0, sizeof(double), s);
+  if (e != cudaSuccess) return e;
+  long long blocks = (n + kStatThreads - 1) / kStatThreads;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  channel_sdr_kernel<<<(unsigned)blocks, kStatThreads, 0, s>>>(mix, mix_stride, src, src_stride, rows, n, out);
+  count_launch();
+  return cudaGetLastError();
+}
+
 }  // namespace bsb

@@ -121,11 +121,17 @@ def metrics_from_stats(stats: torch.Tensor, n: int):
 def train_infer(model: BSRNN, sample, window: Optional[torch.Tensor] = None):
     """Forward-only mirror of m_dataset.train_infer(model, None, sample, L1Loss) (m_dataset.py:202-226), the
     body of train.py's no_grad validation loop (train.py:132-152): returns (loss, sdr, sdr2, sdr3) as
-    0-dim float64 CUDA tensors. sample = (mixture [C,L], speech [C,L]) float32 CUDA tensors (the reference's
-    leading batch-1 dimension is accepted and squeezed, m_dataset.py:184-185).
+    0-dim float64 CUDA tensors. sample = (mixture, speech) float32 CUDA tensors, either [1,C,L] as the reference's
+    DataLoader (batch_size=1, train.py:84-85) hands them over, or [C,L].
+    sdr2 follows the reference's reduction literally: it sums over `dim=1` of the UN-squeezed sample
+    (m_dataset.py:219-222), which for [1,C,L] is the channel axis -- a mean over the L samples of a channel-summed
+    log ratio (bsb_channel_sdr) -- and for a [C,L] sample the time axis (per-row SDR of the mixture, mean over rows).
     All reductions run on the device in one pass per pair (no torchmetrics)."""
     waveform, speech = sample
-    if waveform.dim() == 3:
+    batched = waveform.dim() == 3
+    if batched:
+        if waveform.shape[0] != 1 or speech.shape[0] != 1:
+            raise RuntimeError("train_infer: the leading batch dimension must be 1 (m_dataset.py:184-185 squeezes it)")
         waveform, speech = waveform.squeeze(0), speech.squeeze(0)
     _check_wav(waveform)
     _check_wav(speech)
@@ -135,13 +141,32 @@ def train_infer(model: BSRNN, sample, window: Optional[torch.Tensor] = None):
     n_t = x_time.shape[1]
     st_time = pair_stats(x_time, speech_time)
     st_freq = pair_stats(x, speech_freq)
-    st_mix = pair_stats(waveform, speech)
+    st_mix = None if batched else pair_stats(waveform, speech)
     l1_time, sdr, sisdr = metrics_from_stats(st_time, n_t)
     # L1(Re) + L1(Im): each a mean over C*1025*T elements = the packed array's sum / (C*1025*T)
     l1_freq = st_freq[:, 0].sum() / (x.shape[0] * (x.shape[1] // 2) * x.shape[2])
     # sdr2 (m_dataset.py:219-222): n2Delta = |speech - mixture|^2: here the "estimate" is the mixture
-    _, sdr2, _ = metrics_from_stats(st_mix, waveform.shape[1])
-    return l1_time + l1_freq, sdr.mean(), sdr2.mean(), sisdr.mean()
+    if batched:
+        sdr2 = channel_sdr(waveform, speech)
+    else:
+        sdr2 = metrics_from_stats(st_mix, waveform.shape[1])[1].mean()
+    return l1_time + l1_freq, sdr.mean(), sdr2, sisdr.mean()
+
+
+def channel_sdr(mixture: torch.Tensor, speech: torch.Tensor) -> torch.Tensor:
+    """mean over samples of 10 log10((sum_c s^2 + 1e-9) / (sum_c (s - m)^2 + 1e-9)) for [C,L] float32 CUDA tensors:
+    the reference's sdr2 on its [1,C,L] samples (m_dataset.py:219-222). 0-dim float64 CUDA tensor."""
+    _check_wav(mixture)
+    _check_wav(speech)
+    if mixture.shape != speech.shape or mixture.device != speech.device:
+        raise RuntimeError("channel_sdr: shapes/devices differ")
+    m, s_ = mixture.contiguous(), speech.contiguous()
+    C, L = m.shape
+    with torch.cuda.device(m.device):
+        out = torch.empty((), dtype=torch.float64, device=m.device)
+        _lib.check(_lib.lib().bsb_channel_sdr(m.data_ptr(), L, s_.data_ptr(), L, C, L, out.data_ptr(), _stream_ptr()),
+                   "bsb_channel_sdr")
+    return out / L
 
 
 class StreamingSeparator:

@@ -154,3 +154,39 @@ def test_plugin_oracle_vs_reference_plugin_loop(golden_dir, oracle_sd):
     dry, _ = O.plugin_run(oracle_sd, left, 0.0)
     assert float(dry[:1024].abs().max()) == 0.0
     assert float((dry[2048:6 * 1024] - left[:4 * 1024]).abs().max()) < 1e-6
+
+
+def test_train_infer_matches_literal_restatement(oracle_sd):
+    """Pins oracle.train_infer to m_dataset.train_infer (m_dataset.py:202-226) restated statement by statement with
+    the torch ops the reference calls, on the sample shape its DataLoader yields ([1, 2, L], train.py:84-85):
+    m_dataset.py itself cannot be imported here (torchmetrics / soundfile are not installed)."""
+    wav, src = O.synth_audio(2, 12000, seed=9)
+    sample = (wav[None], src[None])
+    # --- m_dataset.infer, lines 182-199 ---
+    waveform, waveform_speech = sample[0].squeeze(0), sample[1].squeeze(0)
+    win = torch.hann_window(2048)
+    w = torch.stft(waveform, n_fft=2048, hop_length=1024, return_complex=True, window=win)
+    w = torch.stack((w.real, w.imag), dim=2)
+    w = w.reshape((w.shape[0], -1, w.shape[3]))
+    x = O.forward(oracle_sd, w)
+    x = x.reshape((2, -1, 2, x.shape[2]))
+    x = torch.complex(x[:, :, 0, :], x[:, :, 1, :])
+    x_time = torch.istft(x, n_fft=2048, hop_length=1024, window=win)
+    sp_freq = torch.stft(waveform_speech, n_fft=2048, hop_length=1024, return_complex=True, window=win)
+    sp_time = waveform_speech[:, :x_time.shape[1]]
+    # --- m_dataset.train_infer, lines 205-226 (discriminator None, lossfn = L1Loss) ---
+    lossfn = torch.nn.L1Loss()
+    loss = lossfn(x_time, sp_time) + lossfn(x.real, sp_freq.real) + lossfn(x.imag, sp_freq.imag)
+    n2s = torch.sum(torch.square(sp_time), dim=1) + 1e-9
+    n2d = torch.sum(torch.square(x_time - sp_time), dim=1) + 1e-9
+    sdr = (10 * torch.log10(n2s / n2d)).mean()
+    n2s = torch.sum(torch.square(sample[1]), dim=1) + 1e-9
+    n2d = torch.sum(torch.square(sample[1] - sample[0]), dim=1) + 1e-9
+    sdr2 = (10 * torch.log10(n2s / n2d)).mean()
+    got = O.train_infer(oracle_sd, sample[0], sample[1])
+    assert abs(got[0] - float(loss)) < 1e-5 * abs(float(loss))
+    assert abs(got[1] - float(sdr)) < 1e-3 and abs(got[2] - float(sdr2)) < 1e-3
+    assert abs(got[3] - float(O.si_sdr(x_time, sp_time).mean())) < 1e-6
+    # the un-batched [C, L] form reduces sdr2 over time instead (dim=1 of a 2-D sample): a different number
+    per_row = O.train_infer(oracle_sd, wav, src)
+    assert abs(per_row[0] - got[0]) < 1e-9 and abs(per_row[2] - got[2]) > 1e-3
