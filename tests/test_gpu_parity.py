@@ -328,13 +328,20 @@ def test_band_axis_tensor_core_lstm_vs_oracle(dev, model, oracle_sd, C, T):
 
 @pytest.mark.parametrize("C,T,with_state", [(1, 2, False), (1, 3, True), (2, 37, True), (3, 130, False), (5, 64, True),
                                              (1, 15, True), (1, 16, False), (2, 17, True), (1, 33, False), (2, 100, True),
-                                             (1, 4, True), (1, 5, False), (1, 9, True), (4, 8, False), (100, 9, True), (50, 21, True), (51, 6, False)])
+                                             (1, 4, True), (1, 5, False), (1, 9, True), (4, 8, False), (100, 9, True), (50, 21, True), (51, 6, False),
+                                             (40, 9, True), (49, 6, False), (33, 5, True),
+                                             (64, 431, False), (64, 431, True), (55, 200, True), (55, 200, False)])
 def test_time_axis_lstm_vs_oracle_with_state(dev, model, oracle_sd, C, T, with_state):
-    """TimewiseLSTM blocks (bsrnn.py:101-128) on the two-layer wavefront kernel (lstm_seq2.cu, 16 sequences per
-    CTA): ragged last group (12, 24, 36, 60 sequences), a full one (48), more CTAs than SMs (1200 sequences ->
-    150 CTAs), both group sizes (8 sequences per CTA up to 592 sequences, 16 beyond: 600 and 612 sequences have a
-    half-empty last group), step counts around the 4-step projection blocks / flag publications and the buffer
-    cycles, initial (h, c) in, final (h, c) out, against the ATen LSTM."""
+    """TimewiseLSTM blocks (bsrnn.py:101-128) on the two-layer wavefront kernel (lstm_seq2.cu) against the ATen LSTM,
+    in all four modes of its dispatch (launch_lstm_seq2; nseq = 12 C sequences, 148 SMs):
+      * 8 sequences per CTA + fused output Linear (3 CTAs per group): nseq <= 392  -> C <= 32
+      * 8 per CTA, separate fc GEMM (2 CTAs per group):               nseq <= 592  -> C = 33..49: (33,5) (40,9) (49,6)
+      * 16 per CTA + fused output Linear:                             nseq <= 784  -> C = 50..65: (50,21) (51,6)
+        and the headline shape itself, cfg 2 = (64, 431): 768 sequences x 431 steps = 108 projection blocks / flag
+        publications / staging-buffer cycles, and (55, 200) = 660 sequences with a ragged last group (4 of 16)
+      * 16 per CTA, separate fc, more CTAs than SMs:                   (100, 9) = 1200 sequences -> 150 CTAs
+    Ragged last groups (12, 24, 36, 60 sequences), step counts around the 4-step projection blocks, initial (h, c)
+    in, final (h, c) out."""
     from speechseparation_b200 import _lib
     l = _lib.lib()
     packed = model.packed_weights(dev)
@@ -351,8 +358,9 @@ def test_time_axis_lstm_vs_oracle_with_state(dev, model, oracle_sd, C, T, with_s
         so = torch.zeros(2, 2, C * 12, 64, device=dev)
         got = _run_block(l, j, fin.reshape(C * T, 12, 64).to(dev), C, T, packed, ws,
                          None if st is None else st.to(dev), so)
-        assert rel(got.reshape(C, T, 12, 64), ref) < 5e-5, (j, C, T)
-        assert float((so[0].cpu() - hn).abs().max()) < 2e-5 and float((so[1].cpu() - cn).abs().max()) < 5e-5
+        tol = 5e-5 if T <= 130 else 1e-4            # 431 recurrent steps accumulate a little more rounding
+        assert rel(got.reshape(C, T, 12, 64), ref) < tol, (j, C, T)
+        assert float((so[0].cpu() - hn).abs().max()) < tol and float((so[1].cpu() - cn).abs().max()) < 2 * tol
 
 
 def test_lstm_saturated_gates_stay_finite(dev, model):
@@ -379,6 +387,109 @@ def test_full_size_properties_cfg2_slice(dev, model):
     sub = model.separate(wav[5:7].contiguous())
     assert rel(sub, out[5:7]) < 1e-5                           # other rows share tiles but not results
     assert float(model.separate(torch.zeros(2, L, device=dev)).abs().max()) == 0.0
+
+
+def test_cfg2_headline_shape_vs_oracle(dev, model, oracle_sd):
+    """BASELINE.json configs[1] exactly -- 64 rows x 10 s (27,584 frame-rows; 768 time-axis sequences x 431 steps in
+    the 16-sequences-per-CTA fused mode; 216 band-axis tiles) -- waveform against the CPU oracle, per row:
+    max|y - y_ref| / max|y_ref| <= 1e-3 and |SI-SDR(y, s) - SI-SDR(y_ref, s)| <= 0.01 dB (north_star gate), plus
+    SI-SDR(y, y_ref) as the figure of how far below the gate the path sits."""
+    wav, src = O.synth_audio(64, 441000, seed=1234)
+    ref = O.separate(oracle_sd, wav)
+    out = model.separate(wav.to(dev)).cpu()
+    assert out.shape == ref.shape == (64, 1024 * 430)
+    y, r = out.double(), ref.double()
+    per_row = (y - r).abs().amax(1) / r.abs().amax(1)
+    assert float(per_row.max()) <= GATE, per_row
+    s = src[:, :out.shape[1]]
+    d_sisdr = (O.si_sdr(out, s) - O.si_sdr(ref, s)).abs()
+    assert float(d_sisdr.max()) <= 0.01, d_sisdr
+    fidelity = O.si_sdr(out, ref)
+    print(f"cfg2 vs oracle: max rel err {float(per_row.max()):.3e}, max |dSI-SDR| {float(d_sisdr.max()):.2e} dB, "
+          f"min SI-SDR(y, y_ref) {float(fidelity.min()):.1f} dB")
+    assert float(fidelity.min()) > 60.0
+    assert float(per_row.max()) <= GATE / 20            # measured ~1e-5: a regression to plain bf16/TF32 would show
+
+
+def test_streaming_1000_hops_vs_oracle(dev, model, oracle_sd):
+    """cfg 3 as SURVEY.md 8(d) specifies it: 2 rows, >= 1000 hops from a zero state. Through StreamingSeparator
+    (two CUDA graphs, state ping-pong from hop 2 on) and through the LADSPA-shaped C++ host, against the oracle's
+    restatement of infer-streaming.py:104-147 / speech-ladspa-onnx.cpp:171-267: waveform gate on the concatenated
+    hops and the carried state after the last hop (drift over ~1000 graph replays)."""
+    from speechseparation_b200 import StreamingSeparator, plugin
+    hops = 1000
+    wav, _ = O.synth_audio(2, hops * 1024, seed=77)
+    ref, ref_state = O.stream(oracle_sd, wav)
+    sep = StreamingSeparator(model, rows=2)
+    dwav = wav.to(dev)
+    got = torch.empty(2, hops * 1024, device=dev)
+    for h in range(hops):
+        got[:, h * 1024:(h + 1) * 1024] = sep.step(dwav[:, h * 1024:(h + 1) * 1024])
+    got = got.cpu()
+    assert O.max_rel_err(got, ref) < GATE / 5
+    assert O.max_rel_err(got[:, -50 * 1024:], ref[:, -50 * 1024:]) < GATE / 5      # the last hops on their own scale
+    assert float((sep.current_state.cpu() - ref_state).abs().max()) < 2e-4
+    assert float((O.si_sdr(got, ref)).min()) > 60.0
+    # the plugin host over the same number of hops (channel 0 only, output delayed by its 1024-sample FIFO)
+    p = plugin.SpeechSeparatorPlugin(oracle_sd, device=dev.index or 0)
+    left = wav[0].numpy().copy()
+    out = p.process(left, mix=1.0, blocks=[1024])
+    pref, pstate = O.plugin_run(oracle_sd, wav[0], 1.0)
+    assert O.max_rel_err(torch.from_numpy(out)[None], pref[None]) < GATE / 5
+    assert float((p.state() - pstate).abs().max()) < 2e-4 and p.hops == hops
+    p.close()
+
+
+def test_forward_unfused_8_sequence_mode_full_model(dev, model, oracle_sd):
+    """C = 40 rows (480 time-axis sequences): the dispatch branch with 8 sequences per CTA whose layer-1 output
+    leaves as bf16 planes for a separate tensor-core fc GEMM -- full forward against the oracle."""
+    rs = np.random.RandomState(4040)
+    x = torch.from_numpy((rs.standard_normal((40, 2050, 7)) * 2.0).astype(np.float32))
+    assert rel(model.forward(x.to(dev)), O.forward(oracle_sd, x)) < STAGE_TOL
+
+
+def test_two_devices_in_one_process(oracle_sd):
+    """The dynamic-shared-memory opt-in and the signal tables are per device: a model on cuda:0 and then one on
+    cuda:1 in the same process must both run (process-wide `static bool attr_set`)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from speechseparation_b200 import BSRNN
+    wav, _ = O.synth_audio(2, 300 * 1024, seed=5)
+    ref = O.separate(oracle_sd, wav)
+    for d in (0, 1, 0):
+        device = torch.device("cuda", d)
+        with contextlib.redirect_stdout(io.StringIO()):
+            m = BSRNN()
+        m.load_state_dict(oracle_sd, strict=True)
+        m = m.to(device).eval()
+        out = m.separate(wav.to(device))
+        assert O.max_rel_err(out.cpu(), ref) < GATE / 5, d
+        y, _ = m.forward_recurrent(torch.randn(2, 2050, device=device), torch.zeros(4, 2, 24, 64, device=device))
+        assert bool(torch.isfinite(y).all())
+
+
+def test_streams_share_packed_weights_safely(dev, model, oracle_sd):
+    """Weights packed on one stream and used at once on another: the consumer stream must wait for
+    the packing kernels, and two streams must not share one workspace."""
+    from speechseparation_b200 import BSRNN
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = BSRNN()
+    m.load_state_dict(oracle_sd, strict=True)
+    m = m.to(dev).eval()
+    wav, _ = O.synth_audio(3, 200 * 1024, seed=8)
+    dwav = wav.to(dev)
+    s1, s2 = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    torch.cuda.synchronize()
+    with torch.cuda.stream(s1):
+        m.packed_weights(dev)                   # packing kernels queued on s1 ...
+    with torch.cuda.stream(s2):
+        a = m.separate(dwav)                    # ... consumed on s2 without a host sync in between
+    with torch.cuda.stream(s1):
+        b = m.separate(dwav)                    # concurrently on s1: its own workspace
+    torch.cuda.synchronize()
+    ref = O.separate(oracle_sd, wav)
+    assert O.max_rel_err(a.cpu(), ref) < GATE / 5 and torch.equal(a, b)
+    assert len(m._ws) == 2
 
 
 def test_batch_separator_pipeline_equals_separate(dev, model):
@@ -465,11 +576,14 @@ def test_train_infer_metrics_vs_oracle(dev, model, oracle_sd):
     """Forward-only m_dataset.train_infer (loss, sdr, sdr2, si-sdr) with every reduction on the device."""
     from speechseparation_b200 import train_infer
     wav, src = O.synth_audio(2, 30000, seed=21)
-    want = O.train_infer(oracle_sd, wav, src)
-    got = [float(v) for v in train_infer(model, (wav.to(dev)[None], src.to(dev)[None]))]
-    assert abs(got[0] - want[0]) < 1e-4 * abs(want[0])
-    for a, b in zip(got[1:], want[1:]):
-        assert abs(a - b) < 0.01, (got, want)            # dB
+    # [1, C, L] as the reference's DataLoader yields it (sdr2 reduces over channels, m_dataset.py:219-222) and [C, L]
+    for batched in (True, False):
+        sample = (wav[None], src[None]) if batched else (wav, src)
+        want = O.train_infer(oracle_sd, *sample)
+        got = [float(v) for v in train_infer(model, tuple(t.to(dev) for t in sample))]
+        assert abs(got[0] - want[0]) < 1e-4 * abs(want[0])
+        for a, b in zip(got[1:], want[1:]):
+            assert abs(a - b) < 0.01, (batched, got, want)            # dB
     with pytest.raises(RuntimeError):
         train_infer(model, (wav, src))                   # host tensors: no CPU path
 
