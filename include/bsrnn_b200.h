@@ -50,6 +50,8 @@ extern "C" {
 #define BSB_E_SHAPE    (-2)   /* shape the path does not accept (e.g. L <= 1024 for reflect pad) */
 #define BSB_E_WORKSPACE (-3)  /* workspace too small */
 #define BSB_E_ALIGN    (-4)   /* pointer not 16-byte aligned where required */
+#define BSB_E_TOO_LARGE (-5)  /* request exceeds a fixed limit (bsb_stft_pack_static: BSB_STATIC_MAX_FRAME_ROWS) */
+#define BSB_STATIC_MAX_FRAME_ROWS 512   /* C*T limit of bsb_stft_pack_static */
 
 /* --- introspection ------------------------------------------------------------------ */
 int         bsb_version(void);
@@ -84,6 +86,18 @@ int bsb_num_frames(long long L);
 /* m_dataset.py:187-190: wav[C][L] -> x[C][2050][T] (boundary layout). ws: workspace. */
 int bsb_stft_pack(const float* wav, int C, long long L, const float* window,
                   float* x, void* ws, size_t ws_bytes, void* stream);
+/* bsb_stft_pack without any allocation: no workspace argument, no cudaMalloc / cudaFree / allocating library call,
+ * ever -- for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it). This entry point has NO counterpart in the reference.
+ * The frame-major scratch that bsb_stft_pack takes from the caller, and the window / twiddle tables,
+ * live in file-scope `static __device__` arrays of csrc/fft.cu (4.03 MB, held by every GPU that loads the library
+ * until the process exits); their device addresses are resolved once per device with cudaGetSymbolAddress.
+ *   limit:   C * T <= BSB_STATIC_MAX_FRAME_ROWS (512 frame-rows), else BSB_E_TOO_LARGE;
+ *   sharing: every call on a device uses the same scratch, which keeps the previous call's contents (nothing in it
+ *            must start at zero: each call writes every float it later reads). Calls whose kernels OVERLAP on the
+ *            GPU (different streams without an ordering between them) race on it -- serialise them.
+ * Same result as bsb_stft_pack, bit for bit. wav[C][L] -> x[C][2050][T]; window as above. */
+int bsb_stft_pack_static(const float* wav, int C, long long L, const float* window, float* x, void* stream);
 /* same analysis, frame-major output xf[C*T][BSB_XS] (internal layout, no transpose) */
 int bsb_stft_frames(const float* wav, int C, long long L, const float* window,
                     float* xf, void* stream);

@@ -29,6 +29,7 @@ SIGNATURES = {
     "bsb_workspace_bytes": (csz, [ci, ci]),
     "bsb_num_frames": (ci, [cll]),
     "bsb_stft_pack": (ci, [cfp, ci, cll, cfp, cfp, vp, csz, vp]),
+    "bsb_stft_pack_static": (ci, [cfp, ci, cll, cfp, cfp, vp]),
     "bsb_stft_frames": (ci, [cfp, ci, cll, cfp, cfp, vp]),
     "bsb_unpack_istft": (ci, [cfp, ci, ci, cfp, cfp, vp, csz, vp]),
     "bsb_istft_frames": (ci, [cfp, ci, ci, cfp, cfp, vp]),

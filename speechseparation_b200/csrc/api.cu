@@ -194,6 +194,7 @@ const char* bsb_error_string(int code) {
     case BSB_E_SHAPE: return "bsrnn_b200: unsupported shape";
     case BSB_E_WORKSPACE: return "bsrnn_b200: workspace too small";
     case BSB_E_ALIGN: return "bsrnn_b200: pointer not 16-byte aligned";
+    case BSB_E_TOO_LARGE: return "bsrnn_b200: C*T exceeds the static scratch of bsb_stft_pack_static (BSB_STATIC_MAX_FRAME_ROWS = 512 frame-rows); use bsb_stft_pack with a workspace";
     default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "bsrnn_b200: unknown error";
   }
 }
@@ -710,6 +711,15 @@ int bsb_channel_sdr(const float* mix, long long mix_stride, const float* src, lo
   if (!mix || !src || !out || rows <= 0 || n <= 0 || mix_stride < n || src_stride < n) return BSB_E_ARG;
   if ((reinterpret_cast<uintptr_t>(out) & 7) != 0) return BSB_E_ALIGN;
   CK(launch_channel_sdr(mix, mix_stride, src, src_stride, rows, n, out, S(stream)));
+  return 0;
+}
+
+int bsb_stft_pack_static(const float* wav, int C, long long L, const float* window, float* x, void* stream) {
+  if (!wav || !x || C <= 0) return BSB_E_ARG;
+  const int T = bsb_num_frames(L);
+  if (T < 1) return BSB_E_SHAPE;
+  if ((long long)C * T > static_max_frame_rows()) return BSB_E_TOO_LARGE;
+  CK(launch_stft_pack_static(wav, C, L, T, window, x, S(stream)));
   return 0;
 }
 

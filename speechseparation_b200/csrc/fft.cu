@@ -593,4 +593,81 @@ cudaError_t launch_from_frames(const float* xf, int xs, int C, int T, float* x, 
   return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------------------------------
+// bsb_stft_pack_static: the STFT + pack of bsb_stft_pack for callers that may not allocate (code under CUDA graph
+// capture, tight serving loops, harnesses that forbid cudaMalloc). No counterpart in the reference.
+// bsb_stft_pack needs a caller workspace for the frame-major spectrum it transposes
+// from, and its window / twiddle tables come from a cudaMalloc on first use; here BOTH live in file-scope __device__
+// arrays: every GPU that loads the library holds them (4.03 MB) until the process exits.
+//   * limit: C * T <= kStaticFrameRows frame-rows (512 = 11.9 s of audio over all rows); larger calls are rejected
+//   * the scratch is shared by every call on a device and keeps the previous call's contents. Nothing in it has to
+//     start at zero: the analysis kernel writes all 2050 floats of every frame-row the transpose reads. Two calls
+//     whose kernels overlap on the GPU (different streams, no ordering between them) RACE on it.
+// In host code the array names below are host-side stand-ins, not device addresses: the launches take the pointers
+// that cudaGetSymbolAddress returned for the current device at set-up.
+constexpr int kStaticFrameRows = 512;
+constexpr int kStaticTw = kM + kM + 1 + 1024;
+static __device__ __align__(256) float g_static_scratch[kStaticFrameRows * kXS];   // frame-major xf[C*T][2052]
+static __device__ __align__(256) float g_static_window[kN];                        // periodic Hann
+static __device__ __align__(256) float2 g_static_tw[kStaticTw];                    // the three twiddle tables (Tables::tw)
+
+namespace {
+struct StaticPtrs {
+  float* scratch = nullptr;
+  float* window = nullptr;
+  float2* tw = nullptr;
+  bool ready = false;
+};
+std::mutex g_static_mu;
+StaticPtrs g_static_ptrs[64];
+
+// once per device, with that device current: resolve the device addresses and upload the constant tables (plain
+// cudaMemcpy to memory the module already owns: no allocation)
+cudaError_t static_setup(StaticPtrs** out) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  StaticPtrs& p = g_static_ptrs[dev];
+  if (!p.ready) {
+    if ((e = cudaGetSymbolAddress((void**)&p.scratch, g_static_scratch)) != cudaSuccess) return e;
+    if ((e = cudaGetSymbolAddress((void**)&p.window, g_static_window)) != cudaSuccess) return e;
+    if ((e = cudaGetSymbolAddress((void**)&p.tw, g_static_tw)) != cudaSuccess) return e;
+    const double pi = 3.14159265358979323846;          // same host arithmetic as ensure_tables: identical tables
+    static float w[kN];
+    static float2 tw[kStaticTw];
+    for (int n = 0; n < kN; ++n) w[n] = (float)(0.5 - 0.5 * std::cos(2.0 * pi * n / kN));
+    for (int k = 0; k < kM; ++k) tw[k] = make_float2((float)std::cos(2.0 * pi * k / kM), (float)-std::sin(2.0 * pi * k / kM));
+    for (int k = 0; k <= kM; ++k) tw[kM + k] = make_float2((float)std::cos(2.0 * pi * k / kN), (float)-std::sin(2.0 * pi * k / kN));
+    for (int k1 = 0; k1 < 32; ++k1)
+      for (int l = 0; l < 32; ++l)
+        tw[kTw32 + k1 * 32 + l] = make_float2((float)std::cos(2.0 * pi * (l * k1) / kM), (float)-std::sin(2.0 * pi * (l * k1) / kM));
+    if ((e = cudaMemcpy(p.window, w, sizeof(w), cudaMemcpyHostToDevice)) != cudaSuccess) return e;
+    if ((e = cudaMemcpy(p.tw, tw, sizeof(tw), cudaMemcpyHostToDevice)) != cudaSuccess) return e;
+    p.ready = true;
+  }
+  *out = &p;
+  return cudaSuccess;
+}
+}  // namespace
+
+int static_max_frame_rows() { return kStaticFrameRows; }
+
+cudaError_t launch_stft_pack_static(const float* wav, int C, long long L, int T, const float* window, float* x,
+                                    cudaStream_t s) {
+  StaticPtrs* p = nullptr;
+  cudaError_t e = static_setup(&p);
+  if (e != cudaSuccess) return e;
+  const int nrows = C * T;
+  stft_warp_kernel<<<(nrows + kFrameWarps - 1) / kFrameWarps, kFrameWarps * 32, 0, s>>>(
+      wav, L, T, nrows, window ? window : p->window, p->tw, p->scratch, kXS);
+  count_launch();
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  dim3 grid((T + 31) / 32, (kSpec + 31) / 32, C);
+  from_frames_kernel<<<grid, 256, 0, s>>>(p->scratch, kXS, T, x);
+  count_launch();
+  return cudaGetLastError();
+}
+
 }  // namespace bsb

@@ -178,6 +178,11 @@ cudaError_t launch_stream_synthesis(const float* y, const float* dry, const floa
 // x[C][2050][T] <-> xf[C*T][xs]
 cudaError_t launch_to_frames(const float* x, int C, int T, float* xf, int xs, cudaStream_t s);
 cudaError_t launch_from_frames(const float* xf, int xs, int C, int T, float* x, cudaStream_t s);
+// wav[C][L] -> x[C][2050][T] through the file-scope __device__ scratch of fft.cu (no workspace, no allocation);
+// C * T <= static_max_frame_rows()
+cudaError_t launch_stft_pack_static(const float* wav, int C, long long L, int T, const float* window, float* x,
+                                    cudaStream_t s);
+int static_max_frame_rows();
 const float* builtin_window(cudaStream_t s, cudaError_t* err);   // device float[2048], periodic Hann
 const float2* twiddle_tables(cudaStream_t s, cudaError_t* err);  // device: [1024] W_1024^k then [1025] W_2048^k
 // creates the window / twiddle tables of the CURRENT device (the library's only device allocation: 28 KB, once per
