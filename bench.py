@@ -32,21 +32,29 @@ WORKLOADS = {
     "cfg2_offline_64x10s": (64, 441000),
     "cfg1_offline_2x4s": (2, 176400),
     "cfg5_longform_1x60s": (1, 2646000),
+    # BASELINE.json configs[3]: 512 streaming sessions x 2 rows = 1,024 rows in TOTAL, sharded over the ranks
+    # (strong scaling); a step is one 1024-sample hop of every session
+    "cfg4_sessions_512": (1024, 1024),
 }
+SESSIONS = "cfg4_sessions_512"
 
 
-def synth(rows: int, n: int, device, seed: int = 1234) -> torch.Tensor:
-    """Synthetic mixture: 150 Hz 5-harmonic AM tone (peak 0.3) + 0.1*randn, different per row."""
+def synth(rows: int, n: int, device, seed: int = 1234, with_source: int = 0):
+    """Synthetic mixture: 150 Hz 5-harmonic AM tone (peak 0.3) + 0.1*randn, different per row.
+    with_source = k: also return the clean source of the first k rows (for the SI-SDR parity figure)."""
     g = torch.Generator(device="cpu").manual_seed(seed)
     t = torch.arange(n, dtype=torch.float64) / SR
     out = torch.empty(rows, n, dtype=torch.float32)
+    src = torch.empty(with_source, n, dtype=torch.float32)
     for r in range(rows):
         f0 = 150.0 * (1.0 + 0.02 * (r % 16))
         s = sum(torch.sin(2 * torch.pi * f0 * (h + 1) * t + 0.7 * h + r) / (h + 1) for h in range(5))
         s = s * (0.6 + 0.4 * torch.sin(2 * torch.pi * 4.0 * t + r))
         s = 0.3 * s / s.abs().max()
         out[r] = (s + 0.1 * torch.randn(n, generator=g, dtype=torch.float64)).float()
-    return out.to(device)
+        if r < with_source:
+            src[r] = s.float()
+    return (out.to(device), src) if with_source else out.to(device)
 
 
 # which kernel runs each timed stage, and how many launches of it the stage holds
@@ -151,27 +159,87 @@ def peaks():
     if os.path.exists(p):
         d = json.load(open(p))
         return {"hbm": d["hbm_gbs"], "tensor": d["bf16_tflops"], "tensor_sustained": d.get("bf16_tflops_sustained"),
-                "src": "measured"}
-    return {"hbm": 6650.0, "tensor": 1590.0, "tensor_sustained": 1400.0, "src": "fallback"}
+                "src": "measured (MEASURED_PEAKS.json)"}
+    return {"hbm": 6650.0, "tensor": 1590.0, "tensor_sustained": 1400.0, "src": "fallback (B200_PROFILING.md)"}
+
+
+def source_stamp() -> str:
+    """sha256 over the kernel sources: ties profiles/r02_traffic.json (ncu DRAM bytes per launch) to the build it was
+    measured on. The GPU box has no .git, so the stamp is computed from the files that travel."""
+    import hashlib
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, "speechseparation_b200", "csrc")
+    for f in sorted(os.listdir(d)):
+        if f.endswith((".cu", ".cuh", ".cpp", ".h")):
+            h.update(f.encode())
+            h.update(open(os.path.join(d, f), "rb").read())
+    return h.hexdigest()[:16]
+
+
+def measured_traffic(kernel: str):
+    """DRAM read+write bytes per launch of `kernel` from the ncu launch list of THIS build
+    (profiles/r02_traffic.json, written by tools/traffic_from_launches.py); (None, reason) when the file is
+    missing or was measured on different kernel sources."""
+    tp = os.path.join(ROOT, "profiles", "r02_traffic.json")
+    if not os.path.exists(tp):
+        return None, "no ncu launch list for this round yet"
+    d = json.load(open(tp))
+    if d.get("source_stamp") != source_stamp():
+        return None, f"stale: measured on sources {d.get('source_stamp')}, this build is {source_stamp()}"
+    return d.get("per_launch_bytes", {}).get(kernel), "ncu dram__bytes_read.sum + dram__bytes_write.sum per launch, same sources"
 
 
 def cpu_baseline(rows: int, n: int, repeats: int = 3):
-    """The oracle (CPU restatement of the reference path = stock PyTorch fp32 ops, what the
-    reference itself runs) on the host cores, on a bounded sample of the workload."""
-    from oracle import bsrnn_oracle as O          # checker/baseline only, never on the product path
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    sd = O.make_state_dict(0)
-    wav = synth(rows, n, "cpu")
-    with torch.no_grad():
-        O.separate(sd, wav[:1, : min(n, 44100)])   # warm-up
-        best = float("inf")
-        for _ in range(repeats):
-            t0 = time.perf_counter()
-            O.separate(sd, wav)
-            best = min(best, time.perf_counter() - t0)
-    return {"value": rows * n / SR / best, "unit": "audio-sec/s", "cores": cores, "kind": "port",
-            "sample": f"{rows} x {n / SR:.1f} s clips, best of {repeats}, oracle/bsrnn_oracle.py (torch {torch.__version__} CPU fp32)"}
+    """The reference (staged oracle/_ref/bsrnn.py inside the restated wrap; else the oracle port) on the host cores,
+    on a bounded sample of the workload: oracle/baselines.py. Checker/baseline only, never on the product path."""
+    from oracle import baselines
+    return baselines.cpu_baseline(synth, rows, n, repeats)
+
+
+def parity_figure(model, wav_rows: torch.Tensor, src_rows: torch.Tensor, out_rows: torch.Tensor):
+    """Rows 0..k-1 of the timed batch through the CPU oracle (rows are independent, bsrnn.py:61,391-395) against the
+    same rows of the GPU result, OUTSIDE the timed region: north_star gate max|y-y_ref|/max|y_ref| <= 1e-3 per row
+    and |dSI-SDR| <= 0.01 dB against the clean synthetic source."""
+    from oracle import bsrnn_oracle as O          # the checker
+    sd = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+    ref = O.separate(sd, wav_rows.cpu())
+    got = out_rows.cpu()
+    err = O.max_rel_err(got, ref)
+    s = src_rows[:, :got.shape[1]]
+    d_si = float((O.si_sdr(got, s) - O.si_sdr(ref, s)).abs().max())
+    return {"rows_checked": int(got.shape[0]), "max_rel_err": err, "d_si_sdr_db": d_si,
+            "si_sdr_vs_oracle_db": float(O.si_sdr(got, ref).min()), "gate": {"max_rel_err": 1e-3, "d_si_sdr_db": 0.01},
+            "ok": bool(err <= 1e-3 and d_si <= 0.01), "oracle": "oracle/bsrnn_oracle.py separate(), CPU fp32"}
+
+
+def host_copy_ceiling(dev, in_bytes: int, out_bytes: int, iters: int = 6):
+    """Bare copy ceiling of this rank's host path: H2D of `in_bytes` and D2H of `out_bytes` from pinned buffers on
+    two streams, concurrently, NO kernels. Returns seconds per (H2D + D2H) pair; bench.py turns the max over ranks
+    into an aggregate GB/s = what the e2e figure could reach if the kernels were free."""
+    hi = torch.empty(in_bytes, dtype=torch.uint8).pin_memory()
+    ho = torch.empty(out_bytes, dtype=torch.uint8).pin_memory()
+    di = torch.empty(in_bytes, dtype=torch.uint8, device=dev)
+    do = torch.empty(out_bytes, dtype=torch.uint8, device=dev)
+    s1, s2 = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    for _ in range(2):
+        with torch.cuda.stream(s1):
+            di.copy_(hi, non_blocking=True)
+        with torch.cuda.stream(s2):
+            ho.copy_(do, non_blocking=True)
+    torch.cuda.synchronize(dev)
+    e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+    e0.record()
+    s1.wait_event(e0)
+    s2.wait_event(e0)
+    for _ in range(iters):
+        with torch.cuda.stream(s1):
+            di.copy_(hi, non_blocking=True)
+        with torch.cuda.stream(s2):
+            ho.copy_(do, non_blocking=True)
+    e1.record(s1)
+    e2.record(s2)
+    torch.cuda.synchronize(dev)
+    return max(e0.elapsed_time(e1), e0.elapsed_time(e2)) / 1e3 / iters
 
 
 def streaming_latency(model, dev, hops: int = 400, rows: int = 2):
@@ -243,32 +311,41 @@ def plugin_latency(model, hops: int = 400):
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the reference's own CPU implementation of the path (stock PyTorch ops,
-    restated in oracle/) on all host cores; each step is a bounded sample of the workload."""
+    """--impl reference: the reference's own CPU implementation of the path on all host cores -- the unmodified
+    bsrnn.BSRNN staged as oracle/_ref/bsrnn.py inside the restated wrap lines (kind "reference"), else the oracle
+    port (kind "port"). A step is the FULL workload of one GPU (cfg 2: all 64 rows, ~1.3 s on 16 cores)."""
     if rank != 0:
         return
-    rows_full, n = WORKLOADS[args.workload]
-    rows = min(rows_full, 4)
-    from oracle import bsrnn_oracle as O
+    rows, n = WORKLOADS[args.workload]
+    from oracle import baselines
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    sd = O.make_state_dict(0)
-    wav = synth(rows, n, "cpu")
+    fwd, fwd_rec, kind = baselines._forward_fn(0, "cpu")
     with torch.no_grad():
-        for _ in range(args.warmup):
-            O.separate(sd, wav)
+        if args.workload == SESSIONS:
+            hop = baselines.stream_hop_fn(fwd_rec, "cpu", rows=rows)
+            chunks = 0.1 * torch.randn(args.warmup + args.steps, rows, 1024)
+            step = lambda i: hop(chunks[i])
+            audio_s = (rows // 2) * 1024 / SR
+        else:
+            wav = synth(rows, n, "cpu")
+            step = lambda i: baselines.separate_with(fwd, wav)
+            audio_s = rows * n / SR
+        for i in range(args.warmup):
+            step(i)
         t0 = time.perf_counter()
-        for _ in range(args.steps):
-            O.separate(sd, wav)
+        for i in range(args.steps):
+            step(args.warmup + i)
         dt = time.perf_counter() - t0
-    val = args.steps * rows * n / SR / dt
-    sample = f"{rows} of {rows_full} rows x {n / SR:.1f} s per step"
+    val = args.steps * audio_s / dt
+    sample = f"all {rows} rows x {n / SR:.3f} s per step (the full per-GPU workload)"
     print(json.dumps({
         "impl": "reference", "metric": "audio-sec separated/sec", "value": val, "unit": "audio-sec/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload, "sample": sample, "device": "cpu"},
-        "cpu_baseline": {"value": val, "unit": "audio-sec/s", "cores": cores, "kind": "port", "sample": sample},
+        "config": {"workload": args.workload, "rows_per_gpu": rows, "clip_s": n / SR, "sample": sample, "device": "cpu",
+                   "weights": "random init, torch.manual_seed(0)"},
+        "cpu_baseline": {"value": val, "unit": "audio-sec/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": val, "unit": "audio-sec/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
 
@@ -425,14 +502,13 @@ def main():
     top = max(kern, key=lambda n_: kern[n_]["ms"])
     K = kern[top]
     # a kernel is HBM-bound if its HBM time at peak exceeds its tensor time at peak
-    tpeak = pk["tensor_sustained"] or pk["tensor"]        # timed inside a long step: the sustained figure
+    # the timed region is well under a second at full clocks: the BURST bf16 figure is the denominator (the
+    # sustained one, taken under a 4 s load at a lower clock, is printed beside it)
+    tpeak = pk["tensor"]
     # (the tensor pipe executes 3 bf16 MMAs per algorithmic fp32 product in the split-bf16 GEMM)
     tensor_ops = 3.0 if top == GEMM else 1.0
     hbm_bound = (K["bytes"] / pk["hbm"] / 1e9) > (tensor_ops * K["flops"] / tpeak / 1e12)
-    traffic = None
-    tp = os.path.join(ROOT, "profiles", "r01_traffic.json")
-    if os.path.exists(tp):
-        traffic = json.load(open(tp)).get(top)
+    traffic, traffic_note = measured_traffic(top)
     if hbm_bound:
         roof = {"bound": "hbm", "achieved": K["gbs"], "peak": pk["hbm"], "unit": "GB/s", "frac": K["hbm_frac"]}
     else:
@@ -443,7 +519,9 @@ def main():
     roof.update({"kernel": top, "launches_per_step": K["launches"], "avg_launch_ms": K["avg_launch_ms"],
                  "algorithmic_flops_per_launch": K["flops"] / K["launches"],
                  "algorithmic_bytes_per_launch": K["bytes"] / K["launches"],
-                 "share_of_step": K["share_of_step"], "traffic": traffic, "peak_source": pk["src"] + " (sustained bf16)"})
+                 "share_of_step": K["share_of_step"], "traffic": traffic, "traffic_source": traffic_note,
+                 "peak_source": pk["src"] + ", burst bf16", "peak_sustained": pk["tensor_sustained"],
+                 "source_stamp": source_stamp()})
     stages = {k: {"ms": v, "tflops": flops[k] * frame_rows / (v / 1e3) / 1e12,
                   "gbs": byt[k] * frame_rows / (v / 1e3) / 1e9} for k, v in stage_ms.items()}
     kernels = {n_: {"ms": round(v["ms"], 4), "launches": v["launches"], "tflops": round(v["tflops"], 2),
