@@ -103,6 +103,7 @@ struct TcArgs {
   int nprob;
   int total_tiles;
   int trace;          // debug builds: this launch records the pipeline timeline
+  int exp;            // timing-experiment switches (g_exp), 0 in production
 };
 
 struct Tile {
@@ -327,8 +328,9 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
           if (piece == 0) {
             // plane block (m-tile, chunk): hi then lo, 16 KB
             const long long aoff = ((long long)(T.m0 / BM) * nk + kc) * (2 * A_PLANE);
+            if (args.exp & 4) { mbar_arrive(bar); } else {
             mbar_arrive_expect_tx(bar, 2 * A_PLANE);
-            bulk_g2s(sb, P.Ah + aoff, 2 * A_PLANE, bar);
+            bulk_g2s(sb, P.Ah + aoff, 2 * A_PLANE, bar); }
           } else {
             // W blocks [bn x 32] bf16, already swizzled: (n0 * nch + kc * bn) * 64 bytes into the plane; a CTA of a
             // pair takes the rows of its half of the tile's columns
@@ -336,8 +338,9 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
             const uint32_t bytes = wrows * (BK * 2);
             const long long off = ((long long)T.n0 * (P.ldw >> 5) + (long long)kc * T.bn + (long long)rank * wrows) * (BK * 2);
             const uint8_t* src = reinterpret_cast<const uint8_t*>(piece == 1 ? P.Wh : P.Wl) + off;
+            if (args.exp & 4) { mbar_arrive(bar); } else {
             mbar_arrive_expect_tx(bar, bytes);
-            bulk_g2s(sb + 2 * A_PLANE + (piece == 2 ? W_PLANE : 0), src, bytes, bar);
+            bulk_g2s(sb + 2 * A_PLANE + (piece == 2 ? W_PLANE : 0), src, bytes, bar); }
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -372,12 +375,14 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
       const int nk = (P.K + BK - 1) / BK;
       mbar_wait(smem_u32(&bar_tempty[acc]), acc_phase ^ 1);   // epilogue has drained this accumulator
       tc_fence_after();
+      if (lane == 0) TRACE(1, 10);
       const uint32_t idesc = make_idesc_bf16(TILE_ROWS, T.bn);
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN_MAX);
       for (int kc = 0; kc < nk; ++kc) {
         mbar_wait(smem_u32(&bar_full[stage]), phase);
         if (PAIR) mbar_wait(smem_u32(&bar_peer[stage]), phase);   // the peer's half of the stage (no data read by this thread)
         tc_fence_after();
+        if (lane == 0) TRACE(1, 11);
         if (elect_one()) {
           const uint32_t sb = smem_base + stage * STAGE_BYTES;
           const uint64_t a_hi = make_sw64_desc(sb);
@@ -392,8 +397,10 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
               mma_bf16_ss_pair(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
               mma_bf16_ss_pair(d_tmem, a_hi + adv, w_hi + adv, idesc, 1);
             } else {
+              if (args.exp & 16) continue;
+              if (!(args.exp & 8)) {
               mma_bf16_ss(d_tmem, a_lo + adv, w_hi + adv, idesc, (kc | kk) != 0);   // small terms first
-              mma_bf16_ss(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
+              mma_bf16_ss(d_tmem, a_hi + adv, w_lo + adv, idesc, 1); }
               mma_bf16_ss(d_tmem, a_hi + adv, w_hi + adv, idesc, 1);
             }
           }
@@ -490,6 +497,7 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
       if (ew == BSB_TRACE_EPI && lane == 0) TRACE(2, 20);
       tc_fence_after();
       const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN_MAX);
+      if (args.exp & 2) cc = ncc;
       for (; cc < ncc; cc += CC_STEP) {
         const int nb = T.n0 + cc * 32;
         uint32_t r[32];
@@ -543,6 +551,7 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
           }
           if (cc + CC_STEP < ncc) fetch(nb + CC_STEP * 32);
         }
+        if (args.exp & 1) { if (v[0] == 123.456f && v[31] == 1.f) orow[0] = v[5]; continue; }
         if (orow) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -557,7 +566,7 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
         }
         if (P.Oh && row) {
           // block (m-tile, 32-column chunk), hi then lo: this step is the whole 64-byte row rt of both
-          const long long blk = ((long long)(T.m0 / BM) * nch_o + (nb >> 5)) * (2 * A_PLANE);
+          const long long blk = ((long long)((args.exp & 32) ? (T.m0 / BM) & 3 : (T.m0 / BM)) * nch_o + (nb >> 5)) * (2 * A_PLANE);
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             uint4 h, l;
@@ -596,6 +605,12 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
 // bit-identical to the single-CTA path but measured slower on this workload (5.2 vs 4.5 ms/step, profiles/
 // r01_summary.md): opt-in for experiments.
 const bool g_pair = getenv("BSB_PAIR") != nullptr;
+// timing experiments only (tools/band_cost.py, tools/exp_cost.py; results are then wrong on purpose):
+// g_band_mask bit i = problem i of a grouped launch takes part;
+// g_exp: 1 = epilogue skips split + stores, 2 = epilogue only releases the accumulator, 4 = loaders skip the bulk
+// copies, 8 = one MMA of three, 16 = no MMAs (commit only), 32 = plane stores go to an L2-resident window
+std::atomic<int> g_band_mask{0xfff};
+std::atomic<int> g_exp{0};
 
 }  // namespace
 
@@ -611,8 +626,9 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
   const int sms = sm_count(dev);
 
   int order[kMaxProb], n = 0;
+  const int mask = g_band_mask.load(std::memory_order_relaxed);
   for (int i = 0; i < args.nprob; ++i)
-    if (args.p[i].K > 0 && args.p[i].M > 0 && args.p[i].N > 0) order[n++] = i;
+    if (args.p[i].K > 0 && args.p[i].M > 0 && args.p[i].N > 0 && ((mask >> i) & 1)) order[n++] = i;
   for (int i = 1; i < n; ++i)               // insertion sort by K descending
     for (int j = i; j > 0 && args.p[order[j]].K > args.p[order[j - 1]].K; --j) {
       const int t = order[j]; order[j] = order[j - 1]; order[j - 1] = t;
@@ -642,6 +658,7 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
   }
   ta.nprob = n;
   ta.total_tiles = total;
+  ta.exp = g_exp.load(std::memory_order_relaxed);
 #ifdef BSB_TRACE
   static int trace_launch = 0, trace_sel = -2;
   if (trace_sel == -2) trace_sel = getenv("BSB_TRACE_LAUNCH") ? atoi(getenv("BSB_TRACE_LAUNCH")) : -1;
@@ -673,6 +690,9 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
   count_launch();
   return cudaGetLastError();
 }
+
+extern "C" int bsb_debug_set_band_mask(int mask) { g_band_mask.store(mask); return 0; }
+extern "C" int bsb_debug_set_exp(int e) { g_exp.store(e); return 0; }
 
 #ifdef BSB_TRACE
 extern "C" int bsb_debug_set_trace(void* p) {
