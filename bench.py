@@ -546,6 +546,25 @@ def main():
     dte = t_e2e0.elapsed_time(t_e2e1) / 1e3
     units_e, tmax_e = aggregate_throughput(audio_s * args.steps, dte, device=dev)
     e2e_check = float((hout[(args.steps - 1) & 1] - out.cpu()).abs().max())      # same result as the resident run
+    # (c) the same pipeline with 16-bit PCM host buffers (what the clips' wav files hold, infer.py:24-27): half the bytes
+    del pipe
+    pipe16 = BatchSeparator(model, rows, n, device=dev, pcm16=True)
+    hin16 = [torch.clamp(torch.round(host_in * 32768.0), -32768, 32767).to(torch.int16).pin_memory() for _ in range(2)]
+    hout16 = [torch.empty(out.shape, dtype=torch.int16).pin_memory() for _ in range(2)]
+    for i in range(2):
+        pipe16.submit(hin16[i], hout16[i])
+    pipe16.join()
+    barrier()
+    t_e2e0.record()
+    pipe16.after(t_e2e0)
+    for i in range(args.steps):
+        pipe16.submit(hin16[i & 1], hout16[i & 1])
+    pipe16.join()
+    t_e2e1.record()
+    barrier()
+    dt16 = t_e2e0.elapsed_time(t_e2e1) / 1e3
+    units_16, tmax_16 = aggregate_throughput(audio_s * args.steps, dt16, device=dev)
+    del pipe16
     # bare copy ceiling of the host path at this N (no kernels): max over ranks of the time of one H2D + D2H pair
     t_copy = host_copy_ceiling(dev, host_in.numel() * 4, host_out.numel() * 4)
     barrier()
@@ -638,6 +657,9 @@ def main():
                 "host_numa_node_rank0": numa_node, "api": "speechseparation_b200.BatchSeparator.submit (H2D | kernels | D2H on three streams, 2 buffer pairs)",
                 "serial_value": units_s / tmax_s, "serial_ms_per_step": 1e3 * tmax_s / args.steps,
                 "max_abs_diff_vs_resident": e2e_check,
+                "pcm16_value": units_16 / tmax_16, "pcm16_ms_per_step": 1e3 * tmax_16 / args.steps,
+                "pcm16_note": "same pipeline with int16 PCM host buffers in and out (BatchSeparator(pcm16=True)): "
+                              f"{host_in.numel() * 2} + {host_out.numel() * 2} bytes per step; fp32 is the default contract",
                 "host_copy_ceiling_gbs": bytes_pair / t_copy_max / 1e9,
                 "host_copy_ceiling_value": world * audio_s / t_copy_max,
                 "host_copy_ceiling_note": "bare cudaMemcpyAsync H2D + D2H of one step's bytes per rank from pinned memory on two "
@@ -669,7 +691,6 @@ def main():
     if world == 1 and not args.no_gpu_comparator:
         try:
             from oracle import baselines
-            del pipe
             model._ws.clear()
             torch.cuda.empty_cache()
             res["gpu_comparator"] = baselines.gpu_comparator(synth, rows, n, dev)

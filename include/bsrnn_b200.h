@@ -111,6 +111,13 @@ int bsb_istft_frames(const float* xf, int C, int T, const float* window,
 int bsb_to_frames(const float* x, int C, int T, float* xf, void* stream);
 int bsb_from_frames(const float* xf, int C, int T, float* x, void* stream);
 
+/* 16-bit PCM at the host-buffer boundary -- what the reference's wav files hold before torchaudio.load turns them into
+ * floats (infer.py:24-27): wav = pcm / 32768 (torchaudio's normalisation, exact), and back
+ * pcm = clamp(rint(wav * 32768), -32768, 32767). Halves the host<->device bytes of bulk separation; fp32 stays the
+ * default contract of every other entry point. n = number of samples (all rows). */
+int bsb_pcm16_to_float(const int16_t* pcm, long long n, float* wav, void* stream);
+int bsb_float_to_pcm16(const float* wav, long long n, int16_t* pcm, void* stream);
+
 /* --- model ------------------------------------------------------------------------------- */
 /* BSRNN.forward (bsrnn.py:385-443): x[C][2050][T] -> y[C][2050][T], y = x * mask. */
 int bsb_forward(const float* x, int C, int T, const void* packed,

@@ -30,6 +30,8 @@ SIGNATURES = {
     "bsb_num_frames": (ci, [cll]),
     "bsb_stft_pack": (ci, [cfp, ci, cll, cfp, cfp, vp, csz, vp]),
     "bsb_stft_pack_static": (ci, [cfp, ci, cll, cfp, cfp, vp]),
+    "bsb_pcm16_to_float": (ci, [vp, cll, cfp, vp]),
+    "bsb_float_to_pcm16": (ci, [cfp, cll, vp, vp]),
     "bsb_stft_frames": (ci, [cfp, ci, cll, cfp, cfp, vp]),
     "bsb_unpack_istft": (ci, [cfp, ci, ci, cfp, cfp, vp, csz, vp]),
     "bsb_istft_frames": (ci, [cfp, ci, ci, cfp, cfp, vp]),

@@ -723,4 +723,16 @@ int bsb_stft_pack_static(const float* wav, int C, long long L, const float* wind
   return 0;
 }
 
+int bsb_pcm16_to_float(const int16_t* pcm, long long n, float* wav, void* stream) {
+  if (!pcm || !wav || n <= 0) return BSB_E_ARG;
+  CK(launch_pcm16_to_float(pcm, n, wav, S(stream)));
+  return 0;
+}
+
+int bsb_float_to_pcm16(const float* wav, long long n, int16_t* pcm, void* stream) {
+  if (!pcm || !wav || n <= 0) return BSB_E_ARG;
+  CK(launch_float_to_pcm16(wav, n, pcm, S(stream)));
+  return 0;
+}
+
 }  // extern "C"

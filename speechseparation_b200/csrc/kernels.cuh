@@ -195,6 +195,9 @@ cudaError_t init_signal_tables();
 cudaError_t launch_pair_stats(const float* est, long long est_stride, const float* ref, long long ref_stride,
                               int rows, long long n, double* stats, cudaStream_t s);
 
+// 16-bit PCM <-> float at the host-buffer boundary (metrics.cu)
+cudaError_t launch_pcm16_to_float(const short* pcm, long long n, float* wav, cudaStream_t s);
+cudaError_t launch_float_to_pcm16(const float* wav, long long n, short* pcm, cudaStream_t s);
 // sum over samples of the channel-summed log ratio of m_dataset.py:219-222 (see metrics.cu)
 cudaError_t launch_channel_sdr(const float* mix, long long mix_stride, const float* src, long long src_stride,
                                int rows, long long n, double* out, cudaStream_t s);

@@ -114,4 +114,60 @@ cudaError_t launch_channel_sdr(const float* mix, long long mix_stride, const flo
   return cudaGetLastError();
 }
 
+// 16-bit PCM <-> float at the host-buffer boundary (what a wav file holds before torchaudio.load, infer.py:24-27):
+// halves the host<->device bytes of the bulk path. in: x = s / 32768 (exactly torchaudio's normalisation);
+// out: s = clamp(rint(x * 32768), -32768, 32767). HBM-bound elementwise passes, 8 samples per thread.
+__global__ void __launch_bounds__(256)
+pcm16_to_float_kernel(const short* __restrict__ pcm, long long n, float* __restrict__ wav) {
+  const long long i8 = ((long long)blockIdx.x * 256 + threadIdx.x) * 8;
+  if (i8 + 8 <= n && ((reinterpret_cast<uintptr_t>(pcm) | reinterpret_cast<uintptr_t>(wav)) & 15) == 0) {
+    const uint4 p = __ldg(reinterpret_cast<const uint4*>(pcm + i8));
+    const unsigned w[4] = {p.x, p.y, p.z, p.w};
+    float o[8];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      o[2 * k] = (float)(short)(w[k] & 0xffffu) * (1.f / 32768.f);
+      o[2 * k + 1] = (float)(short)(w[k] >> 16) * (1.f / 32768.f);
+    }
+    *reinterpret_cast<float4*>(wav + i8) = make_float4(o[0], o[1], o[2], o[3]);
+    *reinterpret_cast<float4*>(wav + i8 + 4) = make_float4(o[4], o[5], o[6], o[7]);
+  } else {
+    for (long long i = i8; i < n && i < i8 + 8; ++i) wav[i] = (float)pcm[i] * (1.f / 32768.f);
+  }
+}
+
+__device__ __forceinline__ unsigned to_pcm16(float x) {
+  const float y = fminf(fmaxf(rintf(x * 32768.f), -32768.f), 32767.f);
+  return (unsigned)(int)y & 0xffffu;
+}
+
+__global__ void __launch_bounds__(256)
+float_to_pcm16_kernel(const float* __restrict__ wav, long long n, short* __restrict__ pcm) {
+  const long long i8 = ((long long)blockIdx.x * 256 + threadIdx.x) * 8;
+  if (i8 + 8 <= n && ((reinterpret_cast<uintptr_t>(pcm) | reinterpret_cast<uintptr_t>(wav)) & 15) == 0) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(wav + i8)), b = __ldg(reinterpret_cast<const float4*>(wav + i8 + 4));
+    uint4 o;
+    o.x = to_pcm16(a.x) | (to_pcm16(a.y) << 16);
+    o.y = to_pcm16(a.z) | (to_pcm16(a.w) << 16);
+    o.z = to_pcm16(b.x) | (to_pcm16(b.y) << 16);
+    o.w = to_pcm16(b.z) | (to_pcm16(b.w) << 16);
+    *reinterpret_cast<uint4*>(pcm + i8) = o;
+  } else {
+    for (long long i = i8; i < n && i < i8 + 8; ++i) pcm[i] = (short)to_pcm16(wav[i]);
+  }
+}
+
+cudaError_t launch_pcm16_to_float(const short* pcm, long long n, float* wav, cudaStream_t s) {
+  const long long blocks = (n + 2047) / 2048;
+  pcm16_to_float_kernel<<<(unsigned)blocks, 256, 0, s>>>(pcm, n, wav);
+  count_launch();
+  return cudaGetLastError();
+}
+cudaError_t launch_float_to_pcm16(const float* wav, long long n, short* pcm, cudaStream_t s) {
+  const long long blocks = (n + 2047) / 2048;
+  float_to_pcm16_kernel<<<(unsigned)blocks, 256, 0, s>>>(wav, n, pcm);
+  count_launch();
+  return cudaGetLastError();
+}
+
 }  // namespace bsb

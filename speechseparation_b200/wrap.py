@@ -269,7 +269,10 @@ class BatchSeparator:
             return self.out
 
     def __init__(self, model: BSRNN, rows: int, samples: int, device=None, depth: int = 2,
-                 window: Optional[torch.Tensor] = None):
+                 window: Optional[torch.Tensor] = None, pcm16: bool = False):
+        """pcm16=True: batches arrive and leave as int16 PCM (what the clips' wav files hold; x = s / 32768 as
+        torchaudio.load normalises them, infer.py:24-27) -- half the host<->device bytes, converted on the device
+        (bsb_pcm16_to_float / bsb_float_to_pcm16). float32 (default) is the reference's tensor contract."""
         dev = torch.device(device) if device is not None else next(model.parameters()).device
         if dev.type != "cuda":
             raise RuntimeError("BatchSeparator needs a CUDA device: speechseparation_b200 has no CPU path")
@@ -279,10 +282,15 @@ class BatchSeparator:
         _check_window(window, dev)
         self.model, self.dev, self.rows, self.samples, self.depth, self.window = model, dev, rows, samples, depth, window
         self.out_samples = HOP * (T - 1)
+        self.pcm16 = bool(pcm16)
+        self.io_dtype = torch.int16 if self.pcm16 else torch.float32
         with torch.cuda.device(dev):
             self.s_in, self.s_run, self.s_out = (torch.cuda.Stream(dev) for _ in range(3))
-            self.d_in = [torch.empty(rows, samples, device=dev) for _ in range(depth)]
-            self.d_out = [torch.empty(rows, self.out_samples, device=dev) for _ in range(depth)]
+            self.d_in = [torch.empty(rows, samples, device=dev, dtype=self.io_dtype) for _ in range(depth)]
+            self.d_out = [torch.empty(rows, self.out_samples, device=dev, dtype=self.io_dtype) for _ in range(depth)]
+            if self.pcm16:      # float staging of one batch (the kernels of consecutive batches run one after the other)
+                self.f_in = torch.empty(rows, samples, device=dev)
+                self.f_out = torch.empty(rows, self.out_samples, device=dev)
             self.ev_in = [torch.cuda.Event() for _ in range(depth)]
             self.ev_run = [torch.cuda.Event() for _ in range(depth)]
             self.ev_out = [torch.cuda.Event() for _ in range(depth)]
@@ -290,8 +298,8 @@ class BatchSeparator:
         self.n = 0
 
     def _check_host(self, t: torch.Tensor, shape, what: str):
-        if t.device.type != "cpu" or t.dtype != torch.float32 or tuple(t.shape) != tuple(shape) or not t.is_contiguous():
-            raise RuntimeError(f"{what} must be a contiguous float32 host tensor of shape {tuple(shape)}")
+        if t.device.type != "cpu" or t.dtype != self.io_dtype or tuple(t.shape) != tuple(shape) or not t.is_contiguous():
+            raise RuntimeError(f"{what} must be a contiguous {self.io_dtype} host tensor of shape {tuple(shape)}")
         if not t.is_pinned():
             raise RuntimeError(f"{what} must be in pinned host memory (torch.empty(..., pin_memory=True))")
 
@@ -316,7 +324,15 @@ class BatchSeparator:
             if self.used[b]:
                 self.s_run.wait_event(self.ev_out[b])         # d_out[b] is free once it reached the host
             with torch.cuda.stream(self.s_run):
-                self.model.separate(self.d_in[b], self.window, out=self.d_out[b])
+                if self.pcm16:
+                    l, sp = _lib.lib(), _stream_ptr()
+                    _lib.check(l.bsb_pcm16_to_float(self.d_in[b].data_ptr(), self.d_in[b].numel(), self.f_in.data_ptr(), sp),
+                               "bsb_pcm16_to_float")
+                    self.model.separate(self.f_in, self.window, out=self.f_out)
+                    _lib.check(l.bsb_float_to_pcm16(self.f_out.data_ptr(), self.f_out.numel(), self.d_out[b].data_ptr(), sp),
+                               "bsb_float_to_pcm16")
+                else:
+                    self.model.separate(self.d_in[b], self.window, out=self.d_out[b])
                 self.ev_run[b].record()
             self.s_out.wait_event(self.ev_run[b])
             with torch.cuda.stream(self.s_out):

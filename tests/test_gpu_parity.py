@@ -509,6 +509,31 @@ def test_batch_separator_pipeline_equals_separate(dev, model):
         pipe.submit(ins[0][:, :-1].contiguous().pin_memory(), outs[0])
 
 
+def test_batch_separator_pcm16_mode(dev, model, oracle_sd):
+    """int16 PCM in and out (half the host<->device bytes): the input is exactly what torchaudio.load would hand
+    the reference for a 16-bit wav (s / 32768), the output is the float result rounded to 16 bits."""
+    from speechseparation_b200 import BatchSeparator
+    C, L = 3, 30000
+    pipe = BatchSeparator(model, C, L, device=dev, pcm16=True)
+    wav, _ = O.synth_audio(C, L, seed=12)
+    pcm = torch.clamp(torch.round(wav * 32768.0), -32768, 32767).to(torch.int16)
+    pcm[0, 0], pcm[0, 1] = -32768, 32767                                   # full-scale samples
+    outs = [torch.empty(C, pipe.out_samples, dtype=torch.int16).pin_memory() for _ in range(3)]
+    tickets = [pipe.submit(pcm.pin_memory(), o) for o in outs]
+    got = [t.wait().clone() for t in tickets]
+    assert torch.equal(got[0], got[1]) and torch.equal(got[1], got[2])
+    x = pcm.float() / 32768.0                                              # torchaudio.load's normalisation
+    ref = O.separate(oracle_sd, x)
+    want = torch.clamp(torch.round(model.separate(x.to(dev)).cpu() * 32768.0), -32768, 32767).to(torch.int16)
+    assert torch.equal(got[0], want)                                       # the conversion kernels, bit for bit
+    # against the oracle: half an LSB of 16-bit rounding (2^-16 of full scale) plus the path's own error. (Relative
+    # to max|y_ref| that can be large: a random-init model's output is far below full scale.)
+    err = (got[0].float() / 32768.0 - ref).abs().max()
+    assert float(err) <= 0.5 / 32768.0 + GATE * float(ref.abs().max())
+    with pytest.raises(RuntimeError):
+        pipe.submit(wav.pin_memory(), outs[0])                             # float tensor into a pcm16 pipe
+
+
 def test_ladspa_plugin_host_vs_golden_and_oracle(dev, oracle_sd, golden_dir, tmp_path):
     """The LADSPA-shaped C++ host (csrc/plugin.cpp) against the reference plugin loop (golden) with ragged
     run() block sizes, three control-port values, graph replay after the second hop, reset, and the

@@ -12,7 +12,7 @@ with contextlib.redirect_stdout(io.StringIO()):
     m = BSRNN().to(dev).eval()
 wav = 0.1 * torch.randn(64, 441000, device=dev)
 out = m.separate(wav)
-exps = {"baseline": 0, "stores to an L2-resident window": 32, "no stores": 1, "no epilogue": 2, "no copies": 4, "1 MMA of 3": 8, "no MMA": 16, "no copies, no epi": 6,
+exps = {"baseline": 0, "stores to an L2-resident window": 32, "split but no plane stores": 64, "no stores": 1, "no epilogue": 2, "no copies": 4, "1 MMA of 3": 8, "no MMA": 16, "no copies, no epi": 6,
         "no copies, no stores": 5, "1 MMA, no epi": 10, "1 MMA, no copies": 12, "only MMA": 6, "nothing but sync": 22}
 l.bsb_set_stage_timing(1)
 for bname, mk in (("band 9", 0x200), ("bands 6-10", 0x7c0), ("all", 0xfff)):
