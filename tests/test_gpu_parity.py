@@ -528,8 +528,11 @@ def test_batch_separator_pcm16_mode(dev, model, oracle_sd):
     assert torch.equal(got[0], want)                                       # the conversion kernels, bit for bit
     # against the oracle: half an LSB of 16-bit rounding (2^-16 of full scale) plus the path's own error. (Relative
     # to max|y_ref| that can be large: a random-init model's output is far below full scale.)
-    err = (got[0].float() / 32768.0 - ref).abs().max()
+    # Samples beyond 16-bit full scale clip, as they would in a PCM wav file.
+    clipped = ref.clamp(-1.0, 32767.0 / 32768.0)
+    err = (got[0].float() / 32768.0 - clipped).abs().max()
     assert float(err) <= 0.5 / 32768.0 + GATE * float(ref.abs().max())
+    assert int((got[0] == 32767).sum()) > 0 or float(ref.max()) < 1.0      # this input does clip
     with pytest.raises(RuntimeError):
         pipe.submit(wav.pin_memory(), outs[0])                             # float tensor into a pcm16 pipe
 
