@@ -21,6 +21,13 @@
 // hidden units each) as soon as all epilogue warps have read a slot, and the x part (N = 64 per MMA) refills
 // it; when h_t is complete only the 12 MMAs of the h part (N = 256) remain before the next epilogue.
 //
+// Persistent grid (round 2): one CTA per SM, the CTAs split between the directions (even CTAs forward, odd reverse)
+// and each walks the 128-sequence tiles of its direction, so the weight image (128-192 KB) is loaded ONCE per SM by
+// four to six 32 KB bulk copies instead of once per tile with plain loads (432 CTAs at cfg 2: ~30-45 us per launch).
+// Inside a step the epilogue keeps the tcgen05.ld of the NEXT 64-column slot and the tcgen05.st of x_{t+1} in
+// flight under the cell arithmetic of the current slot (measured before: with no MMAs and no cell arithmetic the
+// launch still took 57-63 % of its time -- four serialised TMEM loads, a TMEM store and their waits per step).
+//
 // Gate rows are permuted to n = 4*unit + gate so a thread reads the four gates of a unit from
 // four adjacent TMEM columns, and pre-scaled by -log2(e) (i,f,o) / -2.log2(e) (g) so the
 // accumulator is directly the ex2 argument. The cell update shares reciprocals
@@ -47,6 +54,11 @@ struct Cfg {
   static constexpr int W_BYTES = 2 * PLANE;
   static constexpr int SMEM = W_BYTES + kGates * 4 + 1024;  // + bias + alignment slack
   static constexpr int XH = KIN / 2;                        // x floats per epilogue thread
+  // keep the tcgen05.ld of the next slot in flight under the cell arithmetic of the current one (second register set)
+#ifndef BSB_LSTM_PIPE128
+#define BSB_LSTM_PIPE128 0
+#endif
+  static constexpr bool PIPE = KIN == 64 || BSB_LSTM_PIPE128;
 };
 
 template <int KIN>
@@ -54,12 +66,16 @@ __global__ void __launch_bounds__(THREADS, 1)
 lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
   using C = Cfg<KIN>;
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bar_ready, bar_full, bar_slot[4];
+  __shared__ __align__(8) uint64_t bar_ready, bar_full, bar_slot[4], bar_w;
   __shared__ uint32_t tmem_slot;
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
-  const int dir = blockIdx.y;
+  // persistent: CTA b serves direction b % ndir and is the (b / ndir)-th of the gridDim.x / ndir CTAs of that direction
+  const int dir = (int)blockIdx.x % a.ndir;
+  const int cta_slot = (int)blockIdx.x / a.ndir;
+  const int cta_slots = (int)gridDim.x / a.ndir;
+  const int ntiles = (a.nseq + TILE - 1) / TILE;
   const bool reverse = dir == 1;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
@@ -68,21 +84,20 @@ lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
   if (tid == 0) {
     mbar_init(smem_u32(&bar_ready), N_EPI_WARPS * 32);
     mbar_init(smem_u32(&bar_full), 1);
+    mbar_init(smem_u32(&bar_w), 1);
     for (int i = 0; i < 4; ++i) mbar_init(smem_u32(&bar_slot[i]), N_EPI_WARPS * 32);
     fence_mbar_init();
+    // weights: the packed image is already the swizzled shared-memory layout; one bulk copy per 32 KB chunk
+    mbar_arrive_expect_tx(smem_u32(&bar_w), C::W_BYTES);
+    const uint8_t* src = reinterpret_cast<const uint8_t*>(a.wimg[dir]);
+    for (int i = 0; i < C::W_BYTES / CHUNK_BYTES; ++i)
+      bulk_g2s(smem_base + i * CHUNK_BYTES, src + (size_t)i * CHUNK_BYTES, CHUNK_BYTES, smem_u32(&bar_w));
   }
   if (warp == N_EPI_WARPS) {
     tmem_alloc(smem_u32(&tmem_slot), 512);
     tmem_relinquish();
   }
-  // weights: the packed image is already the swizzled shared-memory layout
-  {
-    const uint4* src = reinterpret_cast<const uint4*>(a.wimg[dir]);
-    uint4* dst = reinterpret_cast<uint4*>(smem_gen);
-    for (int i = tid; i < C::W_BYTES / 16; i += THREADS) dst[i] = __ldg(src + i);
-    for (int i = tid; i < kGates; i += THREADS) bias_s[i] = __ldg(a.bias[dir] + i);
-  }
-  fence_proxy_async_smem();
+  for (int i = tid; i < kGates; i += THREADS) bias_s[i] = __ldg(a.bias[dir] + i);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -92,9 +107,11 @@ lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
     // ================= epilogue / operand producer =================
     const int q = warp & 3, hf = warp >> 2;
     const int row = q * 32 + lane;
-    const long long seq = (long long)blockIdx.x * TILE + row;
-    const bool valid = seq < a.nseq;
     const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16);
+    uint32_t g = 0;                           // steps done by this CTA: the barrier phases run on across tiles
+    for (int tile = cta_slot; tile < ntiles; tile += cta_slots) {
+    const long long seq = (long long)tile * TILE + row;
+    const bool valid = seq < a.nseq;
     const float* xrow = a.x + seq * a.x_seq + hf * C::XH;
     float* hrow = a.hout + seq * a.h_seq + dir * kFeat + hf * 8;
 
@@ -128,7 +145,8 @@ lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
 #pragma unroll
     for (int i = 0; i < 32; ++i) c[i] = 0.f;
 
-    // round 0: x of the first step; nothing to wait for, h_{-1} = 0
+    // round 0 of a tile: x of the first step; h_{-1} = 0. (Every MMA of the previous tile has completed: its last
+    // bar_full was waited for, so the x columns and the accumulator are free.)
     load_x(reverse ? a.nsteps - 1 : 0);
     store_x();
     tmem_st_wait();
@@ -137,23 +155,32 @@ lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
     for (int sl = 0; sl < 4; ++sl) mbar_arrive(smem_u32(&bar_slot[sl]));
     mbar_arrive(smem_u32(&bar_ready));
 
-    for (int it = 0; it < a.nsteps; ++it) {
+    for (int it = 0; it < a.nsteps; ++it, ++g) {
       const int step = reverse ? a.nsteps - 1 - it : it;
       const bool more = it + 1 < a.nsteps;
       if (more) load_x(reverse ? step - 1 : step + 1);       // in flight while the MMAs run
-      mbar_wait(smem_u32(&bar_full), it & 1);
+      mbar_wait(smem_u32(&bar_full), g & 1);
       tc_fence_after();
-      if (more) {                                            // all MMAs of this step are done: the x columns are free
+      // slot = 16 units = 64 accumulator columns, 8 units (32 columns) per thread. The load of slot sl + 1 is issued
+      // before the arithmetic of slot sl, and the store of x_{t+1} (all MMAs of this step are done: the x columns
+      // are free) runs under the load of slot 0.
+      uint32_t ra[32], rb[C::PIPE ? 32 : 1];
+      if (!C::PIPE && more) {                                // (KIN = 128: no registers to spare for the overlap)
         store_x();
         tmem_st_wait();
       }
+      tmem_ld_32x32(tlane + COL_ACC + hf * 32, ra);
+      if (C::PIPE && more) store_x();
       float* hdst = hrow + (long long)step * a.h_step;
 #pragma unroll
-      for (int sl = 0; sl < 4; ++sl) {                       // slot = 16 units = 64 accumulator columns; 8 units here
-        uint32_t r[32];
-        tmem_ld_32x32(tlane + COL_ACC + sl * 64 + hf * 32, r);
+      for (int sl = 0; sl < 4; ++sl) {
+        uint32_t (&r)[32] = (C::PIPE && (sl & 1)) ? reinterpret_cast<uint32_t (&)[32]>(rb) : ra;
+        uint32_t (&rn)[32] = (C::PIPE && !(sl & 1)) ? reinterpret_cast<uint32_t (&)[32]>(rb) : ra;
+        if (!C::PIPE && sl > 0) tmem_ld_32x32(tlane + COL_ACC + sl * 64 + hf * 32, r);
         tmem_ld_wait32(r);
-        if (more) {                                          // this thread is done with the slot (and x_{t+1} is in place)
+        if (C::PIPE && sl == 0 && more) tmem_st_wait();      // x_{t+1} is in place
+        if (C::PIPE && sl < 3) tmem_ld_32x32(tlane + COL_ACC + (sl + 1) * 64 + hf * 32, rn);
+        if (more) {                                          // this thread is done with the slot
           tc_fence_before();
           mbar_arrive(smem_u32(&bar_slot[sl]));
         }
@@ -182,9 +209,9 @@ lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
             // A operand of the Linear that follows (kernels.cuh planes: [m-tile][32-column chunk][128 x 64 B]): row
             // seq*nsteps + step; units 16 sl + 8 hf .. +7 of direction dir = chunk 2 dir + sl/2, 16-byte unit 2 (sl&1) + hf
             const long long m = seq * a.nsteps + step;
-            const int r = (int)(m & 127);
+            const int r128 = (int)(m & 127);
             uint8_t* p = reinterpret_cast<uint8_t*>(a.hplanes) + ((m >> 7) * (2 * a.ndir) + 2 * dir + (sl >> 1)) * (2 * kPlaneBlock) +
-                         sw64(r, 2 * (sl & 1) + hf);
+                         sw64(r128, 2 * (sl & 1) + hf);
             *reinterpret_cast<uint4*>(p) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
             *reinterpret_cast<uint4*>(p + a.hp_lo) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
           } else {
@@ -204,14 +231,18 @@ lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
         mbar_arrive(smem_u32(&bar_ready));
       }
     }
+    }
   } else {
     // ================= MMA issuer =================
     const uint32_t idesc_slot = make_idesc_bf16(TILE, 64);
     const uint32_t idesc_full = make_idesc_bf16(TILE, kGates);
     const uint32_t d_tmem = tmem_base + COL_ACC;
     constexpr int NCX = C::NCH - 1;                          // K chunks of the x part
-    for (int it = 0; it < a.nsteps; ++it) {
-      const uint32_t par = it & 1;
+    mbar_wait(smem_u32(&bar_w), 0);                          // the weight image has landed (once per CTA)
+    uint32_t g = 0;
+    for (int tile = cta_slot; tile < ntiles; tile += cta_slots)
+    for (int it = 0; it < a.nsteps; ++it, ++g) {
+      const uint32_t par = g & 1;
       // x part of this step, slot by slot as the epilogue of the previous step releases the accumulator
       for (int sl = 0; sl < 4; ++sl) {
         mbar_wait(smem_u32(&bar_slot[sl]), par);
@@ -273,8 +304,14 @@ cudaError_t launch_kin(const LstmTcArgs& a, cudaStream_t s) {
   static SmemOptIn opt;
   cudaError_t e = opt_in_smem(lstm_tc_kernel<KIN>, Cfg<KIN>::SMEM, opt);
   if (e != cudaSuccess) return e;
-  dim3 grid((a.nseq + TILE - 1) / TILE, a.ndir);
-  lstm_tc_kernel<KIN><<<grid, THREADS, Cfg<KIN>::SMEM, s>>>(a);
+  if (a.ndir < 1 || a.ndir > 2) return cudaErrorInvalidValue;
+  // persistent: one CTA per SM, an equal number per direction, no more than there are tiles
+  int dev = 0;
+  if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+  const int ntiles = (a.nseq + TILE - 1) / TILE;
+  int per_dir = sm_count(dev) / a.ndir;
+  if (per_dir > ntiles) per_dir = ntiles;
+  lstm_tc_kernel<KIN><<<per_dir * a.ndir, THREADS, Cfg<KIN>::SMEM, s>>>(a);
   count_launch();
   return cudaGetLastError();
 }
