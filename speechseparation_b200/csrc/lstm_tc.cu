@@ -18,8 +18,9 @@
 //
 // Only W_hh.h_{t-1} is on the serial path. The W_ih'.x_t half of step t+1 is issued while the epilogue of
 // step t is still running: the accumulator is handed back to the tensor core in four 64-column slots (16
-// hidden units each) as soon as all epilogue warps have read a slot, and the x part (N = 64 per MMA) refills
-// it; when h_t is complete only the 12 MMAs of the h part (N = 256) remain before the next epilogue.
+// hidden units each) as soon as all epilogue warps have read a slot, and the x part refills it in two halves of
+// two slots (N = 128 per MMA); when h_t is complete only the 12 MMAs of the h part (N = 256) remain before
+// the next epilogue.
 //
 // Persistent grid (round 2): one CTA per SM, the CTAs split between the directions (even CTAs forward, odd reverse)
 // and each walks the 128-sequence tiles of its direction, so the weight image (128-192 KB) is loaded ONCE per SM by
@@ -234,7 +235,7 @@ lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
     }
   } else {
     // ================= MMA issuer =================
-    const uint32_t idesc_slot = make_idesc_bf16(TILE, 64);
+    const uint32_t idesc_half = make_idesc_bf16(TILE, 128);
     const uint32_t idesc_full = make_idesc_bf16(TILE, kGates);
     const uint32_t d_tmem = tmem_base + COL_ACC;
     constexpr int NCX = C::NCH - 1;                          // K chunks of the x part
@@ -243,9 +244,13 @@ lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
     for (int tile = cta_slot; tile < ntiles; tile += cta_slots)
     for (int it = 0; it < a.nsteps; ++it, ++g) {
       const uint32_t par = g & 1;
-      // x part of this step, slot by slot as the epilogue of the previous step releases the accumulator
-      for (int sl = 0; sl < 4; ++sl) {
-        mbar_wait(smem_u32(&bar_slot[sl]), par);
+      // x part of this step, in two halves of 128 accumulator columns (32 units) as the epilogue of the previous step
+      // releases them (slot barriers 0,1 then 2,3). N = 128 per MMA: a tcgen05.mma has a floor of ~82 cycles
+      // whatever its N (tools/mma_sw_bench.cu: N = 64 -> 85 cycles, N = 128 -> 90, N = 256 -> 134), so the former
+      // slot-wise N = 64 issue cost 8.2k cycles per step for KIN = 128 -- more than the epilogue it hides under.
+      for (int hv = 0; hv < 2; ++hv) {
+        mbar_wait(smem_u32(&bar_slot[2 * hv]), par);
+        mbar_wait(smem_u32(&bar_slot[2 * hv + 1]), par);
         tc_fence_after();
         if (lane == 0) {
           uint32_t accumulate = 0;
@@ -253,15 +258,15 @@ lstm_tc_kernel(const __grid_constant__ LstmTcArgs a) {
           for (int ch = 0; ch < NCX; ++ch) {
             const uint32_t a_hi0 = tmem_base + COL_AX + ch * 32;
             const uint32_t a_lo0 = a_hi0 + KIN / 2;
-            // rows 64 sl .. 64 sl + 63 of the weight chunk: 8 swizzle atoms of 8 rows x 128 B further
-            const uint64_t w_hi = make_sw128_desc(smem_base + ch * CHUNK_BYTES + sl * 64 * 128);
-            const uint64_t w_lo = make_sw128_desc(smem_base + C::PLANE + ch * CHUNK_BYTES + sl * 64 * 128);
+            // rows 128 hv .. 128 hv + 127 of the weight chunk: 16 swizzle atoms of 8 rows x 128 B further
+            const uint64_t w_hi = make_sw128_desc(smem_base + ch * CHUNK_BYTES + hv * 128 * 128);
+            const uint64_t w_lo = make_sw128_desc(smem_base + C::PLANE + ch * CHUNK_BYTES + hv * 128 * 128);
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk) {
               const uint64_t adv = (uint64_t)(kk * 32 >> 4);   // 16 bf16 = 32 bytes along K
-              mma_bf16_ts(d_tmem + sl * 64, a_lo0 + kk * 8, w_hi + adv, idesc_slot, accumulate);   // small terms first
-              mma_bf16_ts(d_tmem + sl * 64, a_hi0 + kk * 8, w_lo + adv, idesc_slot, 1);
-              mma_bf16_ts(d_tmem + sl * 64, a_hi0 + kk * 8, w_hi + adv, idesc_slot, 1);
+              mma_bf16_ts(d_tmem + hv * 128, a_lo0 + kk * 8, w_hi + adv, idesc_half, accumulate);   // small terms first
+              mma_bf16_ts(d_tmem + hv * 128, a_hi0 + kk * 8, w_lo + adv, idesc_half, 1);
+              mma_bf16_ts(d_tmem + hv * 128, a_hi0 + kk * 8, w_hi + adv, idesc_half, 1);
               accumulate = 1;
             }
           }
