@@ -8,30 +8,33 @@
 //   A_hi.W_hi + A_hi.W_lo + A_lo.W_hi      (fp32 accumulation in TMEM)
 // which reproduces the fp32 path to ~1e-5 end to end at 3 bf16 MMAs per product.
 //
-// Persistent, warp-specialised CTA (one per SM), tiles of 128 rows x up to 256 columns:
-//   8 warps    A producers : fp32 global (512-byte runs per warp request) -> registers, one K chunk
-//                            ahead of the smem stage -> (hi, lo) bf16 (integer rounding on the ALU pipe,
-//                            ptx.cuh split2) -> 128B-swizzled smem
-//   1 warp     W loader    : the weights are packed as ready-made swizzled [bn x 64] bf16 blocks
-//                            (pack.cu), so one thread fetches a hi and a lo block per K chunk with
-//                            cp.async.bulk (TMA engine, completes on the stage's mbarrier)
-//   1 warp     MMA issuer  : one thread issues tcgen05.mma (M=128, N<=256, K=16) x 12 per 64-wide
-//                            K chunk; tcgen05.commit frees the smem stage / publishes the tile
-//   4 warps    epilogue    : tcgen05.ld TMEM -> registers -> per-warp smem transpose, then bias +
-//                            LeakyReLU (+residual, *x) on rows of 32 consecutive columns so that every
-//                            global load/store of the epilogue is a full 128-byte line; the residual /
-//                            mask operands of a chunk are all requested before the TMEM read
-// Two smem stages (mbarrier full/empty ring) and two 256-column TMEM accumulators (full/empty
-// barriers) let producer, tensor core and epilogue overlap across K chunks and across tiles.
+// Persistent, warp-specialised CTA (one per SM), tiles of 128 rows x up to 256 columns, K chunks of 32 (one 64-byte
+// SWIZZLE_64B row = two k-steps of 16 = six MMAs), FOUR shared-memory stages of 48 KB (A hi|lo 16 KB + W hi 16 KB +
+// W lo 16 KB), two 256-column fp32 accumulators in tensor memory:
+//   A from planes (12 of the 14 launch kinds, 384 threads): activations between Linears live in HBM as bf16 hi/lo
+//     "planes" in exactly the shared-memory image (kernels.cuh LinProb::Ap), so a stage is three bulk copies
+//     (cp.async.bulk) issued by three loader warps; warp 0 issues the MMAs (elect.sync, tcgen05.commit frees the
+//     stage); warps 4-11 are the epilogue (two per TMEM lane quarter, alternate 32-column steps).
+//   A from fp32 rows (after the STFT and after the last LSTM block, 768 threads): two groups of 8 producer warps load
+//     rows (16-byte __ldg), split them to bf16 hi/lo on the ALU pipe and store the swizzled stage; 4 epilogue warps
+//     with registers moved to them by setmaxnreg.
+//   Epilogue: tcgen05.ld gives a lane one accumulator row, 32 columns per step: bias, LeakyReLU, "+ residual",
+//     "* multiplier" (operands requested one step ahead), then fp32 rows and/or planes. Plane output of launches
+//     without residual/multiplier operands goes through a 4 KB staging buffer per warp and leaves as two 2 KB
+//     cp.async.bulk shared -> global copies issued by one lane.
 //
-// What bounds it (round-1 measurements, tools/mma_bench*.cu, tools/trace_tc.py, profiles/):
-// tcgen05.mma itself runs at 128-142 cycles per M128xN256xK16 instruction in this operand pattern,
-// also under concurrent LDG/STS/bulk-copy traffic, i.e. 1.7k cycles per chunk; the pipeline
-// delivers a chunk every ~5k cycles. Each chunk makes the SM pull 32 KB of A and 64 KB of W
-// through L2 (the weights are re-streamed for every 128-row tile); deeper A prefetch, fully
-// coalesced loads, cheaper conversion and SMSP placement of the roles all left that period
-// unchanged, a TMEM-resident A operand (lstm_tc.cu style) lost more to row-per-thread loads than
-// it saved. The remaining lever is the CTA pair (cta_group::2: half of W per SM) - next round.
+// What bounds it (round-2 measurements; tools/mma_sw_bench.cu, tools/exp_cost.py, tools/band_cost.py,
+// profiles/r02_summary.md): a tcgen05.mma M128 x N256 x K16 takes 134 cycles with SWIZZLE_64B as with SWIZZLE_128B
+// operands (807 per chunk), but has a floor of ~82 cycles whatever N (N = 64: 85, N = 128: 90), so narrow layers pay
+// 2.6x per MAC. With the epilogue switched off the main loop runs close to that bound; with it, a d -> d layer takes
+// 187 us against ~110 us of MMA time. The cost of the epilogue is proportional to the work it does (split arithmetic
+// and stores ~45 us each of a 410 us pair of launches) and does NOT respond to how it is scheduled: coalescing its
+// stores through shared memory, stores into an L2-resident window, pipelining its TMEM loads, bias from registers,
+// sixteen epilogue warps instead of eight, a boustrophedon tile order and the CTA-pair kernel were all measured at
+// +-1 % or worse; every variant that ADDS shared-memory traffic is slower (+5 .. +70 % on the launch). The shared
+// memory port carries the MMA operand reads (12 KB per MMA = 92 B/clk at full rate) and the bulk-copy writes
+// (48 KB per chunk = 60 B/clk): that sum, not the tensor pipe and not HBM, is what the kernel sits on. The step is
+// also power-capped when sustained (sw_power_cap active, 1.6 GHz inside these launches under ncu).
 #include <cstdlib>
 #include "kernels.cuh"
 #include "ptx.cuh"
