@@ -139,7 +139,7 @@ struct LstmSeq2Args {
   int n_inner, nseq, nsteps;
   void* hplanes;             // optional: layer-1 h as bf16 hi/lo planes instead of fp32 rows at hout
   long long hp_lo;
-  int* flags;                // [2 * groups] ints of scratch (zeroed by the launch)
+  int* flags;                // [2 * groups + 1] ints of scratch (zeroed by the launch): publication flags, CTA ticket counter
   int group;                 // sequences per CTA (8 or 16), chosen by the launch
   // optional: the block's output Linear + residual fused as a third CTA per group: fc_out = W_fc . h_layer1 + b + x
   const float* fcw;          // fp32 [64][ldfcw]

@@ -262,7 +262,15 @@ lstm_seq2_kernel(const __grid_constant__ LstmSeq2Args a) {
   const int tid = threadIdx.x;
   const int w = tid >> 5, lane = tid & 31;
   const int nrole = a.fuse_fc ? 3 : 2;
-  const int layer = blockIdx.x % nrole, grp = blockIdx.x / nrole;      // role 0/1 = LSTM layer, 2 = output Linear
+  // Logical CTA index = a ticket taken at start, not blockIdx.x: layer-1 and fc CTAs spin on flags published by the
+  // CTA with the next-lower logical index of their group. With tickets that producer has always STARTED before its
+  // consumer, whatever order the hardware dispatches CTAs in and even when the grid exceeds the SM count (the unfused
+  // 16-sequence mode: 150 CTAs at 1,200 sequences), so a resident consumer can never wait on a CTA that has no SM.
+  __shared__ int ticket_s;
+  if (tid == 0) ticket_s = atomicAdd(a.flags + 2 * a.ngroups, 1);
+  __syncthreads();
+  const int cta = ticket_s;
+  const int layer = cta % nrole, grp = cta / nrole;                    // role 0/1 = LSTM layer, 2 = output Linear
   const uint32_t smem_base0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   if (layer == 2) {
     fc_role(a, grp, smem_raw + (smem_base0 - smem_u32(smem_raw)), smem_base0);
@@ -621,7 +629,7 @@ cudaError_t launch_lstm_seq2(const LstmSeq2Args& a, cudaStream_t s, int* fused) 
   b.group = group;
   b.fuse_fc = fuse;
   b.ngroups = groups;
-  e = cudaMemsetAsync(a.flags, 0, sizeof(int) * 2 * groups, s);
+  e = cudaMemsetAsync(a.flags, 0, sizeof(int) * (2 * groups + 1), s);      // publication flags + the CTA ticket counter
   if (e != cudaSuccess) return e;
   lstm_seq2_kernel<<<(fuse ? 3 : 2) * groups, THREADS, SMEM_BYTES, s>>>(b);
   if (fused) *fused = fuse;
