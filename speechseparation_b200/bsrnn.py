@@ -81,17 +81,37 @@ def _p(t: Optional[torch.Tensor]):
 
 
 class _ForwardOnly(torch.autograd.Function):
-    """Runs the CUDA forward; backward is not part of this path (north_star is inference)."""
+    """Runs the CUDA forward. The hand-written path has no backward kernels (north_star is inference; SURVEY.md 8(f)
+    rank 4 is not built): by default a gradient request raises. With ``model.backward_mode = "library"`` (opt-in) the
+    backward pass RECOMPUTES the forward graph with stock PyTorch CUDA ops over the module's own parameters
+    (cuBLAS / cuDNN -- library kernels, not this repo's) and differentiates that, so that the reference's train.py
+    (train.py:98-115) can take optimizer steps; the forward values still come from the B200 kernels."""
 
     @staticmethod
     def forward(ctx, model, x, *params):
+        ctx.model = model
+        ctx.save_for_backward(x)
         return model._forward_impl(x)
 
     @staticmethod
-    def backward(ctx, *grads):
-        raise NotImplementedError(
-            "speechseparation_b200.BSRNN is forward-only: the B200 kernels implement the separation "
-            "forward pass (BASELINE.json north_star); no backward is provided. Run under torch.no_grad().")
+    def backward(ctx, grad_y):
+        model = ctx.model
+        if model.backward_mode != "library":
+            raise NotImplementedError(
+                "speechseparation_b200.BSRNN is forward-only: the B200 kernels implement the separation "
+                "forward pass (BASELINE.json north_star); no backward kernels are provided. Run under torch.no_grad(), "
+                "or opt in to the stock-PyTorch recompute with `model.backward_mode = \"library\"`.")
+        (x,) = ctx.saved_tensors
+        params = list(model.parameters())
+        with torch.enable_grad():
+            xg = x.detach().requires_grad_(ctx.needs_input_grad[1])
+            y = model._library_graph(xg)
+            wanted = ([xg] if ctx.needs_input_grad[1] else []) + [p for p in params if p.requires_grad]
+            got = torch.autograd.grad(y, wanted, grad_y, allow_unused=True) if wanted else ()
+        it = iter(got)
+        gx = next(it) if ctx.needs_input_grad[1] else None
+        gp = [next(it) if p.requires_grad else None for p in params]
+        return (None, gx, *gp)
 
 
 class BSRNN(nn.Module):
@@ -120,7 +140,39 @@ class BSRNN(nn.Module):
         self.bandFCs_back_post = nn.ModuleList([
             (nn.Sequential(nn.Linear(x * 2, x * 2), lrelu(), nn.Linear(x * 2, x * 2))
              if x > 0 else nn.Sequential(TrainableConstantModule([0]))) for x in band_split[0]])
+        # "raise" (default): the path is forward-only. "library": backward recomputes through stock PyTorch ops.
+        self.backward_mode = "raise"
         self._reset_caches()
+
+    def _library_graph(self, x: torch.Tensor) -> torch.Tensor:
+        """BSRNN.forward as a differentiable graph of stock PyTorch ops over this module's parameters (used ONLY by
+        the opt-in backward; values agree with the kernels to ~1e-5). Same arithmetic as reference bsrnn.py:385-443:
+        per-band MLPs on [C,T,d], four residual LSTM blocks on [C,T,12,64], decoder MLPs, residual, real multiply."""
+        C, _, T = x.shape
+        dims = [2 * w for w in generate_bandsplits()[0]]
+        xt = x.transpose(1, 2)                                           # [C, T, 2050]
+        residual, feats, off = [], [], 0
+        for i, d in enumerate(dims):
+            if d == 0:                                                   # band 11: learned constant feature
+                residual.append(None)
+                feats.append(self.bandFCs[i][0].trainable_constant.expand(C, T, band_features))
+                continue
+            r = self.bandFCs_pre[i](xt[:, :, off:off + d])
+            residual.append(r)
+            feats.append(self.bandFCs[i](r))
+            off += d
+        z = torch.stack(feats, 2)                                        # [C, T, 12, 64]
+        for j, block in enumerate(self.lstms):
+            m = block.m
+            seq = z.reshape(C * T, len(dims), band_features) if j % 2 == 0 else \
+                z.transpose(1, 2).reshape(C * len(dims), T, band_features)
+            h, _ = m.rnn(m.fc_in(seq))
+            seq = m.fc(h) + seq
+            z = seq.reshape(C, T, len(dims), band_features) if j % 2 == 0 else \
+                seq.reshape(C, len(dims), T, band_features).transpose(1, 2)
+        masks = [residual[i] + self.bandFCs_back_post[i](self.bandFCs_back[i](z[:, :, i]))
+                 for i, d in enumerate(dims) if d > 0]
+        return x * torch.cat(masks, 2).transpose(1, 2)
 
     def _reset_caches(self):
         self._packed: Optional[torch.Tensor] = None
@@ -140,6 +192,7 @@ class BSRNN(nn.Module):
 
     def __setstate__(self, d):
         super().__setstate__(d)
+        self.__dict__.setdefault("backward_mode", "raise")
         self._reset_caches()
 
     def _apply(self, fn, *a, **kw):       # .to() / .cuda() / .float(): parameter storage is replaced

@@ -233,6 +233,45 @@ def test_grad_request_raises_not_silent(dev, oracle_sd):
             y.sum().backward()
 
 
+def test_opt_in_library_backward_matches_oracle_autograd(dev, oracle_sd):
+    """SURVEY 8(f) rank 4 is not built as kernels; the opt-in `backward_mode = "library"` recomputes the graph with
+    stock PyTorch CUDA ops so that train.py can step. Forward values still come from the B200 kernels; the gradients
+    must equal autograd through the CPU oracle on the same weights and input."""
+    from speechseparation_b200 import BSRNN
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = BSRNN()
+    m.load_state_dict(oracle_sd, strict=True)
+    m = m.to(dev).train()
+    m.backward_mode = "library"
+    rs = np.random.RandomState(77)
+    x = torch.from_numpy(rs.standard_normal((2, 2050, 9)).astype(np.float32))
+    wgt = torch.from_numpy(rs.standard_normal((2, 2050, 9)).astype(np.float32))
+    with torch.enable_grad():
+        xd = x.to(dev).requires_grad_(True)
+        y = m.forward(xd)
+        (y * wgt.to(dev)).sum().backward()
+        sd = {k: v.clone().requires_grad_(True) for k, v in oracle_sd.items()}
+        xc = x.clone().requires_grad_(True)
+        yo = O.forward(sd, xc)
+        (yo * wgt).sum().backward()
+    assert rel(y, yo) < STAGE_TOL                                      # forward: the kernels
+    assert rel(xd.grad, xc.grad) < 2e-4
+    worst = 0.0
+    for (k, p), (k2, q) in zip(m.state_dict(keep_vars=True).items(), sd.items()):
+        assert k == k2
+        if p.numel() == 0:
+            continue
+        assert p.grad is not None and q.grad is not None, k
+        worst = max(worst, rel(p.grad, q.grad))
+    assert worst < 5e-4, worst
+    # an optimizer step through the kernels' weight cache: the packed weights are rebuilt, the output changes
+    opt = torch.optim.AdamW(m.parameters(), lr=1e-3)
+    opt.step()
+    with torch.no_grad():
+        y2 = m.forward(x.to(dev))
+    assert not torch.equal(y2, y.detach()) and bool(torch.isfinite(y2).all())
+
+
 def test_repack_after_weight_update(dev, oracle_sd):
     from speechseparation_b200 import BSRNN
     with contextlib.redirect_stdout(io.StringIO()):
