@@ -318,17 +318,32 @@ __device__ __forceinline__ float rcp_approx(float x) {
 }
 
 // ---- fp32 -> (hi, lo) bf16 split: x ~= hi + lo with |x - hi - lo| <= 2^-17 |x| -------------------
-// Integer rounding (add half an ulp, keep the upper 16 bits) on the ALU pipe: the cvt.rn.bf16x2.f32
-// form (F2FP) issues on the quarter-rate XU pipe it shares with MUFU, and ncu showed that pipe 92 %
-// busy with conversions alone in the GEMM producers. Ties round away from zero instead of to even;
-// inputs are finite activations/weights.
+// bf16_round_bits: integer rounding (add half an ulp, keep the upper 16 bits) on the ALU pipe; ties round away from
+// zero instead of to even; inputs are finite activations/weights.
 __device__ __forceinline__ uint32_t bf16_round_bits(float x) { return __float_as_uint(x) + 0x8000u; }
+__device__ __forceinline__ uint32_t cvt_bf16x2(float upper, float lower) {     // two floats -> packed bf16 pair, RNE
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(upper), "f"(lower));
+  return r;
+}
+// (a, b) -> hi = {bf16(b), bf16(a)}, lo = {bf16(b - hi_b), bf16(a - hi_a)}.
+// Packed converts (F2FP: 6 instructions per pair) against integer rounding (~10 per pair on the ALU pipe). Round 1
+// moved the fp32-row PRODUCERS of the GEMM off F2FP because it issues on the quarter-rate XU pipe (92 % busy with
+// conversions there); in the epilogues, whose cost follows their instruction count (profiles/r02_summary.md), the
+// shorter form wins: A/B on one box in profiles/r02_summary.md. -DBSB_SPLIT_INT selects the integer form.
 __device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
+#ifdef BSB_SPLIT_INT
   const uint32_t ra = bf16_round_bits(a), rb = bf16_round_bits(b);
   hi = __byte_perm(ra, rb, 0x7632);                    // {upper half of rb, upper half of ra}
   const float la = a - __uint_as_float(ra & 0xffff0000u);
   const float lb = b - __uint_as_float(rb & 0xffff0000u);
   lo = __byte_perm(bf16_round_bits(la), bf16_round_bits(lb), 0x7632);
+#else
+  hi = cvt_bf16x2(b, a);
+  const float la = a - __uint_as_float(hi << 16);
+  const float lb = b - __uint_as_float(hi & 0xffff0000u);
+  lo = cvt_bf16x2(lb, la);
+#endif
 }
 // single value: the two 16-bit patterns
 __device__ __forceinline__ void split1(float a, uint16_t& hi, uint16_t& lo) {
