@@ -190,7 +190,7 @@ __device__ __forceinline__ void store_a(const AChunk& a, uint8_t* a_hi, uint8_t*
   }
 }
 
-__device__ __forceinline__ float lrelu(float v) { return v > 0.f ? v : v * 0.01f; }
+__device__ __forceinline__ float lrelu(float v) { return fmaxf(v, v * 0.01f); }   // slope < 1: same value as v > 0 ? v : 0.01 v, two instructions
 
 #ifndef BSB_TRACE_EPI
 #define BSB_TRACE_EPI 0     // which epilogue warp the trace follows
