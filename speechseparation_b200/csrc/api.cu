@@ -134,6 +134,7 @@ void set_prob(LinProb& P, const void* packed, const Lin& l, const float* A, int 
   P.act = act;
   P.tile_start = 0; P.tiles_n = 0;
   P.Ap = nullptr; P.Op = nullptr; P.Rp = nullptr; P.a_lo = P.o_lo = P.r_lo = 0;
+  P.o_tail_pad = 0;
 }
 
 // Linear -> Linear activations as bf16 planes (tensor-core path): band i of a layer whose bands are n[0..10]
@@ -332,6 +333,7 @@ int run_bandsplit(const float* xf, int ldx, int rows, const void* packed, float*
   for (int i = 0; i < kRealBands; ++i) {
     set_prob(g.p[i], packed, L.pre[i][1], w.bufA + kBandOff[i], kXS, rrows + kBandOff[i], kXS, rows, ACT_LRELU);
     if (pm) { from_planes(g.p[i], p_pre0, i); to_planes(g.p[i], p_res, i, residual != nullptr); }
+    if (i == kRealBands - 1) g.p[i].o_tail_pad = kXS - kSpec;          // the row's own padding follows band 10
   }
   CK(launch_grouped_linear(g, s));
   mark("pre", s);
@@ -505,6 +507,7 @@ int run_decode(const float* feat, const float* residual, const float* xf, int ld
              rrows + kBandOff[i], kXS, xf + kBandOff[i], ldx);
     if (pm) from_planes(g.p[i], p_p0, i);
     if (residual == nullptr) res_planes(g.p[i], p_rres, i);
+    if (i == kRealBands - 1 && ldy == kXS) g.p[i].o_tail_pad = kXS - kSpec;
   }
   CK(launch_grouped_linear(g, s));
   mark("post_mask", s);

@@ -61,6 +61,8 @@ struct LinProb {
   long long a_lo, o_lo;
   const void* Rp;      // optional: the residual operand as planes of the output's geometry (then res is null)
   long long r_lo;
+  int o_tail_pad;      // floats after column N-1 of every O row that may be overwritten (row padding owned by nobody else):
+                       // lets a 16-byte-granular TMA store serve an N that is not a multiple of 4 (band 10: 514 + 2 of kXS)
 };
 constexpr int kMaxProb = 12;
 constexpr int kPlaneK = 32;                                              // columns per plane block = K chunk of the GEMM

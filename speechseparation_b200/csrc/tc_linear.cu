@@ -36,6 +36,7 @@
 // (48 KB per chunk = 60 B/clk): that sum, not the tensor pipe and not HBM, is what the kernel sits on. The step is
 // also power-capped when sustained (sw_power_cap active, 1.6 GHz inside these launches under ncu).
 #include <cstdlib>
+#include <cuda.h>              // CUtensorMap types only: the encoder is fetched with cudaGetDriverEntryPoint (no libcuda link)
 #include "kernels.cuh"
 #include "ptx.cuh"
 
@@ -106,6 +107,7 @@ struct TcProb {
   int lda, ldw, ldo, ldres, ldmul;
   int M, N, K, act;
   int tile_start, tiles_m;
+  int o_tma;                 // maps.o[problem] is valid: fp32 output rows leave through staging + 2-D TMA stores
 };
 struct TcArgs {
   TcProb p[kMaxProb];
@@ -114,6 +116,12 @@ struct TcArgs {
   int stage_out;      // plane output through the per-warp staging buffers + bulk stores (the launch reserved them)
   int trace;          // debug builds: this launch records the pipeline timeline
   int exp;            // timing-experiment switches (g_exp), 0 in production
+};
+
+// Tensor maps of a launch (second kernel parameter): per problem the fp32 output matrix as a 2-D tensor
+// [M rows][N columns], row pitch ldo, boxes of 32 rows x 32 columns (= 128 B: one SWIZZLE_128B span).
+struct TcMaps {
+  alignas(64) CUtensorMap o[kMaxProb];
 };
 
 struct Tile {
@@ -223,7 +231,7 @@ __device__ unsigned long long* g_trace = nullptr;
 //   bar_tfull[a]  accumulator a complete (commit multicast) bar_tempty[a] (rank 0) drained by all 16 epilogue warps
 template <bool A_PLANES, bool PAIR>
 __global__ void __launch_bounds__(Roles<A_PLANES>::THREADS, 1)
-tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
+tc_grouped_linear_kernel(const __grid_constant__ TcArgs args, const __grid_constant__ TcMaps maps) {
   static_assert(A_PLANES || !PAIR, "the CTA-pair kernel takes its A operand from planes");
   using R = Roles<A_PLANES>;
   constexpr int MMA_WARP = R::MMA_WARP, W_WARP = R::LOAD_WARP, EPI_WARP0 = R::EPI_WARP0, N_EPI_WARPS = R::N_EPI_WARPS;
@@ -564,7 +572,22 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args) {
           if (cc + CC_STEP < ncc) fetch(nb + CC_STEP * 32);
         }
         if (args.exp & 1) { if (v[0] == 123.456f && v[31] == 1.f) orow[0] = v[5]; continue; }
-        if (orow) {
+        if (P.O != nullptr && P.o_tma) {
+          // fp32 rows through the staging buffer ([32 rows][128 B], SWIZZLE_128B: unit j of row r at j ^ (r & 7)) and
+          // ONE 2-D TMA store of the 32 x 32 box; rows >= M / columns >= N are clipped by the hardware
+          if (lane == 0) bulk_wait_read();
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(stg + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+                make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&maps.o[T.pi], stg_s, nb, T.m0 + q * 32);
+            bulk_commit();
+          }
+        } else if (orow) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             const int n = nb + 4 * j;
@@ -653,6 +676,33 @@ std::atomic<int> g_exp{0};
 
 }  // namespace
 
+namespace {
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled() {
+  static EncodeTiledFn fn = []() -> EncodeTiledFn {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+      return nullptr;
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
+  return fn;
+}
+// fp32 matrix [rows][cols] with row pitch ld (floats) as boxes of 32 x 32; false when TMA's alignment rules do not hold
+bool make_map_f32(CUtensorMap* m, const float* base, int rows, int cols, int ld) {
+  EncodeTiledFn enc = encode_tiled();
+  if (!enc || base == nullptr || (reinterpret_cast<uintptr_t>(base) & 15) != 0 || (ld & 3) != 0 || cols < 1 || rows < 1) return false;
+  const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(float)};
+  const cuuint32_t box[2] = {32, 32};
+  const cuuint32_t estr[2] = {1, 1};
+  return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+}  // namespace
+
 // Launch the problems of `args` that have K > 0 on the tensor-core kernel. Problems are taken
 // in descending-K order so that the static round-robin schedule ends with the cheap tiles.
 cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
@@ -674,15 +724,17 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
     }
   TcArgs ta{};
   int total = 0, n_planes = 0;
-  bool rm = false, planes_out = false;
+  bool rm = false, planes_out = false, rows_out = false;
   for (int i = 0; i < n; ++i) {
     const LinProb& L = args.p[order[i]];
     n_planes += L.Ap != nullptr;
     rm = rm || L.res != nullptr || L.mul != nullptr || L.Rp != nullptr;
     planes_out = planes_out || L.Op != nullptr;
+    rows_out = rows_out || L.O != nullptr;
   }
   // (the fp32-row-fed kernel keeps direct stores too: measured pre.0 236 -> 250 us, back.0 86 -> 99 us with staging)
-  const bool stage_out = planes_out && !rm && n_planes != 0;
+  const bool stage_out = (planes_out || rows_out) && !rm && n_planes != 0;
+  TcMaps maps;
   const int extra = stage_out ? EPI_STAGE_TOTAL : 0;
   if (n_planes != 0 && n_planes != n) return cudaErrorInvalidValue;   // one A source per launch
   const bool pair = n_planes != 0 && g_pair;                      // plane operands: CTA pairs, 256-row tiles
@@ -700,6 +752,9 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
     P.bias = L.bias; P.O = L.O; P.res = L.res; P.mul = L.mul;
     P.lda = L.lda; P.ldw = L.ldw64; P.ldo = L.ldo; P.ldres = L.ldres; P.ldmul = L.ldmul;
     P.M = L.M; P.N = L.N; P.K = L.K; P.act = L.act;
+    // (a TMA store moves whole 16-byte units: the extent must be a multiple of 4 floats, or run into padding the row owns)
+    const int n4 = (L.N + 3) & ~3;
+    P.o_tma = (stage_out && L.O != nullptr && n4 - L.N <= L.o_tail_pad && make_map_f32(&maps.o[i], L.O, L.M, n4, L.ldo)) ? 1 : 0;
     P.tile_start = total;
     P.tiles_m = (L.M + tile_rows - 1) / tile_rows;
     total += P.tiles_m * ((L.N + BN_MAX - 1) / BN_MAX);
@@ -727,15 +782,15 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
     at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    e = cudaLaunchKernelEx(&cfg, tc_grouped_linear_kernel<true, true>, ta);
+    e = cudaLaunchKernelEx(&cfg, tc_grouped_linear_kernel<true, true>, ta, maps);
     count_launch();
     return e != cudaSuccess ? e : cudaGetLastError();
   }
   const int grid = total < sms ? total : sms;
   if (n_planes)
-    tc_grouped_linear_kernel<true, false><<<grid, Roles<true>::THREADS, smem_bytes<false>() + extra, s>>>(ta);
+    tc_grouped_linear_kernel<true, false><<<grid, Roles<true>::THREADS, smem_bytes<false>() + extra, s>>>(ta, maps);
   else
-    tc_grouped_linear_kernel<false, false><<<grid, Roles<false>::THREADS, smem_bytes<false>() + extra, s>>>(ta);
+    tc_grouped_linear_kernel<false, false><<<grid, Roles<false>::THREADS, smem_bytes<false>() + extra, s>>>(ta, maps);
   count_launch();
   return cudaGetLastError();
 }
