@@ -108,6 +108,7 @@ struct TcProb {
   int M, N, K, act;
   int tile_start, tiles_m;
   int o_tma;                 // maps.o[problem] is valid: fp32 output rows leave through staging + 2-D TMA stores
+  int ops_tma;               // the residual / multiplier operands of this problem arrive through staging (TMA loads)
 };
 struct TcArgs {
   TcProb p[kMaxProb];
@@ -122,6 +123,8 @@ struct TcArgs {
 // [M rows][N columns], row pitch ldo, boxes of 32 rows x 32 columns (= 128 B: one SWIZZLE_128B span).
 struct TcMaps {
   alignas(64) CUtensorMap o[kMaxProb];
+  alignas(64) CUtensorMap r[kMaxProb];     // "+ residual" operand as fp32 rows
+  alignas(64) CUtensorMap m[kMaxProb];     // "* multiplier" operand (fp32 rows)
 };
 
 struct Tile {
@@ -229,15 +232,23 @@ __device__ unsigned long long* g_trace = nullptr;
 //   bar_full[s]   own bulk copies of stage s landed        bar_peer[s] (rank 0)  rank 1's stage s landed (relayed by its warp 0)
 //   bar_empty[s]  MMAs reading stage s retired (commit multicast to both CTAs)
 //   bar_tfull[a]  accumulator a complete (commit multicast) bar_tempty[a] (rank 0) drained by all 16 epilogue warps
-template <bool A_PLANES, bool PAIR>
+// RMS ("residual / multiplier, staged"): the instantiation for plane-fed launches whose epilogue has a "+ residual" or
+// "* multiplier" operand (post.2, the RNN blocks' fc): three main-loop stages, 8 KB of staging per epilogue warp, the
+// operands brought in by TMA. Kept out of the other instantiations on purpose: compiled into the common kernel (runtime
+// stage count, the extra epilogue code at the 168-register cap) it cost the launches that do not use it 4-5 %.
+template <bool A_PLANES, bool PAIR, bool RMS = false>
 __global__ void __launch_bounds__(Roles<A_PLANES>::THREADS, 1)
 tc_grouped_linear_kernel(const __grid_constant__ TcArgs args, const __grid_constant__ TcMaps maps) {
   static_assert(A_PLANES || !PAIR, "the CTA-pair kernel takes its A operand from planes");
+  static_assert(!RMS || (A_PLANES && !PAIR), "staged operands: plane-fed single-CTA launches only");
   using R = Roles<A_PLANES>;
   constexpr int MMA_WARP = R::MMA_WARP, W_WARP = R::LOAD_WARP, EPI_WARP0 = R::EPI_WARP0, N_EPI_WARPS = R::N_EPI_WARPS;
   constexpr int STAGES = Smem<PAIR>::STAGES, STAGE_BYTES = Smem<PAIR>::STAGE_BYTES, W_PLANE = Smem<PAIR>::W_PLANE;
+  constexpr int nst = RMS ? 3 : STAGES;                           // stages in use
+  constexpr int STG_BYTES = RMS ? 2 * EPI_STAGE_BYTES : EPI_STAGE_BYTES, Y_OFF = RMS ? EPI_STAGE_BYTES : 0;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bar_full[MAX_STAGES], bar_empty[MAX_STAGES], bar_peer[MAX_STAGES], bar_tfull[2], bar_tempty[2];
+  __shared__ __align__(8) uint64_t bar_ld[8];              // per epilogue warp: its staged operand loads have landed
   __shared__ uint32_t tmem_slot;
   const int rank = PAIR ? (int)cluster_ctarank() : 0;
   const int tile0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;          // first tile and stride of this CTA / pair
@@ -256,6 +267,7 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args, const __grid_const
       mbar_init(smem_u32(&bar_empty[s]), 1);
       mbar_init(smem_u32(&bar_peer[s]), 1);
     }
+    for (int i = 0; i < 8; ++i) mbar_init(smem_u32(&bar_ld[i]), 1);
     for (int a = 0; a < 2; ++a) {
       mbar_init(smem_u32(&bar_tfull[a]), 1);
       mbar_init(smem_u32(&bar_tempty[a]), PAIR ? 2 * N_EPI_WARPS : N_EPI_WARPS * 32);   // pair: one lane per epilogue warp of both CTAs
@@ -360,7 +372,7 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args, const __grid_const
             mbar_arrive_expect_tx(bar, bytes);
             bulk_g2s(sb + 2 * A_PLANE + (piece == 2 ? W_PLANE : 0), src, bytes, bar); }
           }
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          if (++stage == nst) { stage = 0; phase ^= 1; }
         }
       }
       }
@@ -377,7 +389,7 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args, const __grid_const
             mbar_wait(smem_u32(&bar_full[stage]), phase);
             mbar_arrive_cluster(map_to_cta(smem_u32(&bar_peer[stage]), 0));
           }
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          if (++stage == nst) { stage = 0; phase ^= 1; }
         }
       }
     } else if (warp == MMA_WARP && rank == 0) {
@@ -431,7 +443,7 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args, const __grid_const
           }
         }
         __syncwarp();
-        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        if (++stage == nst) { stage = 0; phase ^= 1; }
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
@@ -449,8 +461,10 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args, const __grid_const
     if (!A_PLANES) setmaxnreg_inc<REGS_EPILOGUE>();
     const int ew = warp - EPI_WARP0;
     const int q = ew & 3;                   // TMEM lane quarter this warp may access (EPI_WARP0 % 4 == 0)
-    uint8_t* const stg = smem_gen + STAGES * STAGE_BYTES + ew * EPI_STAGE_BYTES;   // plane staging (args.stage_out only)
-    const uint32_t stg_s = smem_base + STAGES * STAGE_BYTES + ew * EPI_STAGE_BYTES;
+    uint8_t* const stg = smem_gen + nst * STAGE_BYTES + ew * STG_BYTES;            // this warp's staging (if the launch reserved it)
+    const uint32_t stg_s = smem_base + nst * STAGE_BYTES + ew * STG_BYTES;
+    const uint32_t bar_l = smem_u32(&bar_ld[ew & 7]);
+    uint32_t ld_phase = 0;                  // phase of bar_l: runs on across the tiles of this warp
     constexpr int CC_STEP = N_EPI_WARPS / 4;
     const int rt = q * 32 + lane;           // row of the tile
     int acc = 0;
@@ -509,9 +523,55 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args, const __grid_const
           }
         }
       };
-      const bool has_rm = rrow != nullptr || mrow != nullptr || res_planes;
+      // Staged operands (P.ops_tma; launches with 8 KB of staging per warp): region R (bytes 0..4095) receives the
+      // residual -- two 2 KB bulk copies of this warp's rows of the hi and lo plane blocks, or one 32 x 32 fp32 box by
+      // 2-D TMA --, region X (4096..8191) the multiplier box. One lane issues them one step ahead (as the per-lane
+      // loads were), completion is counted on the warp's mbarrier; the rows are then read back conflict-free
+      // (SWIZZLE_64B planes / SWIZZLE_128B boxes). No LSU global load, no dependence on L1.
+      const bool ops_tma = RMS && P.ops_tma != 0;
+      auto fetch_staged = [&](int nb) {
+        if (lane == 0) {
+          const uint32_t bytes = ((P.Rh != nullptr || P.res != nullptr) ? 4096u : 0u) + (P.mul != nullptr ? 4096u : 0u);
+          mbar_arrive_expect_tx(bar_l, bytes);
+          if (P.Rh != nullptr) {
+            const long long blk = ((long long)(T.m0 / BM) * nch_o + (nb >> 5)) * (2 * A_PLANE) + q * 2048;
+            bulk_g2s(stg_s, P.Rh + blk, 2048, bar_l);
+            bulk_g2s(stg_s + 2048, P.Rl + blk, 2048, bar_l);
+          } else if (P.res != nullptr) {
+            tma_load_2d(stg_s, &maps.r[T.pi], nb, T.m0 + q * 32, bar_l);
+          }
+          if (P.mul != nullptr) tma_load_2d(stg_s + 4096, &maps.m[T.pi], nb, T.m0 + q * 32, bar_l);
+        }
+      };
+      auto consume_staged = [&]() {          // staging -> this lane's own row in pr[] / pm[] (same layout as fetch())
+        if (lane == 0) mbar_wait(bar_l, ld_phase);
+        ld_phase ^= 1;
+        __syncwarp();
+        if (P.Rh != nullptr) {
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            pr[u] = *reinterpret_cast<const float4*>(stg + sw64(lane, u));
+            pr[4 + u] = *reinterpret_cast<const float4*>(stg + 2048 + sw64(lane, u));
+          }
+        } else if (P.res != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) pr[j] = *reinterpret_cast<const float4*>(stg + lane * 128 + ((j ^ (lane & 7)) << 4));
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) pr[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        if (P.mul != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) pm[j] = *reinterpret_cast<const float4*>(stg + 4096 + lane * 128 + ((j ^ (lane & 7)) << 4));
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) pm[j] = make_float4(1.f, 1.f, 1.f, 1.f);
+        }
+        __syncwarp();                        // every lane has read: the regions may be refilled
+      };
+      const bool has_rm = P.res != nullptr || P.mul != nullptr || P.Rh != nullptr;      // warp-uniform
       int cc = ew >> 2;
-      if (has_rm && cc < ncc) fetch(T.n0 + cc * 32);
+      if (has_rm && cc < ncc) { if (ops_tma) fetch_staged(T.n0 + cc * 32); else fetch(T.n0 + cc * 32); }
       if (lane == 0) mbar_wait(smem_u32(&bar_tfull[acc]), acc_phase);
       __syncwarp();
       if (ew == BSB_TRACE_EPI && lane == 0) TRACE(2, 20);
@@ -538,7 +598,8 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args, const __grid_const
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] += __uint_as_float(r[j]);
         }
-        if (res_planes) {
+        if (ops_tma && has_rm) consume_staged();
+        if (res_planes || (ops_tma && P.Rh != nullptr)) {
           auto bf2 = [](float hbits, float lbits, float& even, float& odd) {     // two bf16 pairs -> hi + lo
             const uint32_t h = __float_as_uint(hbits), l = __float_as_uint(lbits);
             even = __uint_as_float(h << 16) + __uint_as_float(l << 16);
@@ -560,7 +621,7 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args, const __grid_const
             v[8 * u + 6] = (v[8 * u + 6] + e3) * pm[2 * u + 1].z;
             v[8 * u + 7] = (v[8 * u + 7] + o3) * pm[2 * u + 1].w;
           }
-          if (cc + CC_STEP < ncc) fetch(nb + CC_STEP * 32);
+          if (cc + CC_STEP < ncc) { if (ops_tma) fetch_staged(nb + CC_STEP * 32); else fetch(nb + CC_STEP * 32); }
         } else if (has_rm) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -569,7 +630,7 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args, const __grid_const
             v[4 * j + 2] = (v[4 * j + 2] + pr[j].z) * pm[j].z;
             v[4 * j + 3] = (v[4 * j + 3] + pr[j].w) * pm[j].w;
           }
-          if (cc + CC_STEP < ncc) fetch(nb + CC_STEP * 32);
+          if (cc + CC_STEP < ncc) { if (ops_tma) fetch_staged(nb + CC_STEP * 32); else fetch(nb + CC_STEP * 32); }
         }
         if (args.exp & 1) { if (v[0] == 123.456f && v[31] == 1.f) orow[0] = v[5]; continue; }
         if (P.O != nullptr && P.o_tma) {
@@ -579,12 +640,12 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args, const __grid_const
           __syncwarp();
 #pragma unroll
           for (int j = 0; j < 8; ++j)
-            *reinterpret_cast<float4*>(stg + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+            *reinterpret_cast<float4*>(stg + Y_OFF + lane * 128 + ((j ^ (lane & 7)) << 4)) =
                 make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            tma_store_2d(&maps.o[T.pi], stg_s, nb, T.m0 + q * 32);
+            tma_store_2d(&maps.o[T.pi], stg_s + Y_OFF, nb, T.m0 + q * 32);
             bulk_commit();
           }
         } else if (orow) {
@@ -706,12 +767,13 @@ bool make_map_f32(CUtensorMap* m, const float* base, int rows, int cols, int ld)
 // Launch the problems of `args` that have K > 0 on the tensor-core kernel. Problems are taken
 // in descending-K order so that the static round-robin schedule ends with the cheap tiles.
 cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
-  static SmemOptIn opt[3];
+  static SmemOptIn opt[3], opt_rms;
   int dev = 0;
   cudaError_t e = opt_in_smem(tc_grouped_linear_kernel<false, false>, smem_bytes<false>() + EPI_STAGE_TOTAL, opt[0], &dev);
   if (e != cudaSuccess) return e;
   if ((e = opt_in_smem(tc_grouped_linear_kernel<true, false>, smem_bytes<false>() + EPI_STAGE_TOTAL, opt[1])) != cudaSuccess) return e;
   if ((e = opt_in_smem(tc_grouped_linear_kernel<true, true>, smem_bytes<true>() + EPI_STAGE_TOTAL, opt[2])) != cudaSuccess) return e;
+  if ((e = opt_in_smem(tc_grouped_linear_kernel<true, false, true>, smem_bytes<false>() + EPI_STAGE_TOTAL, opt_rms)) != cudaSuccess) return e;
   const int sms = sm_count(dev);
 
   int order[kMaxProb], n = 0;
@@ -733,11 +795,19 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
     rows_out = rows_out || L.O != nullptr;
   }
   // (the fp32-row-fed kernel keeps direct stores too: measured pre.0 236 -> 250 us, back.0 86 -> 99 us with staging)
-  const bool stage_out = (planes_out || rows_out) && !rm && n_planes != 0;
+  const bool pair_req = n_planes != 0 && g_pair;
+  // launches with "+ residual" / "* multiplier" operands: 3 main-loop stages + 8 KB of staging per epilogue warp
+  // ([R | X or Y]); the others: 4 stages + 4 KB ([planes or Y])
+  const bool rm_stage = rm && n_planes != 0 && !pair_req;
+  bool any_mul = false;
+  for (int i = 0; i < n; ++i) any_mul = any_mul || args.p[order[i]].mul != nullptr;
+  const bool reserve = rm_stage || ((planes_out || rows_out) && !rm && n_planes != 0);
+  const int stages = rm_stage ? 3 : Smem<false>::STAGES;
+  const int stg_bytes = rm_stage ? 2 * EPI_STAGE_BYTES : EPI_STAGE_BYTES;
+  const int extra = (reserve ? 8 * stg_bytes : 0) - (Smem<false>::STAGES - stages) * Smem<false>::STAGE_BYTES;
   TcMaps maps;
-  const int extra = stage_out ? EPI_STAGE_TOTAL : 0;
   if (n_planes != 0 && n_planes != n) return cudaErrorInvalidValue;   // one A source per launch
-  const bool pair = n_planes != 0 && g_pair;                      // plane operands: CTA pairs, 256-row tiles
+  const bool pair = pair_req;                                     // plane operands: CTA pairs, 256-row tiles
   const int tile_rows = pair ? 2 * BM : BM;
   for (int i = 0; i < n; ++i) {
     const LinProb& L = args.p[order[i]];
@@ -752,9 +822,14 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
     P.bias = L.bias; P.O = L.O; P.res = L.res; P.mul = L.mul;
     P.lda = L.lda; P.ldw = L.ldw64; P.ldo = L.ldo; P.ldres = L.ldres; P.ldmul = L.ldmul;
     P.M = L.M; P.N = L.N; P.K = L.K; P.act = L.act;
-    // (a TMA store moves whole 16-byte units: the extent must be a multiple of 4 floats, or run into padding the row owns)
+    // (a TMA store moves whole 16-byte units: the extent must be a multiple of 4 floats, or run into padding the row owns;
+    // in a residual/multiplier launch the output shares its staging region with the multiplier box)
     const int n4 = (L.N + 3) & ~3;
-    P.o_tma = (stage_out && L.O != nullptr && n4 - L.N <= L.o_tail_pad && make_map_f32(&maps.o[i], L.O, L.M, n4, L.ldo)) ? 1 : 0;
+    P.o_tma = (reserve && L.O != nullptr && n4 - L.N <= L.o_tail_pad && !(rm_stage && any_mul) &&
+               make_map_f32(&maps.o[i], L.O, L.M, n4, L.ldo)) ? 1 : 0;
+    const bool has_ops = L.res != nullptr || L.mul != nullptr || L.Rp != nullptr;
+    P.ops_tma = (rm_stage && has_ops && (L.res == nullptr || make_map_f32(&maps.r[i], L.res, L.M, L.N, L.ldres)) &&
+                 (L.mul == nullptr || make_map_f32(&maps.m[i], L.mul, L.M, L.N, L.ldmul))) ? 1 : 0;
     P.tile_start = total;
     P.tiles_m = (L.M + tile_rows - 1) / tile_rows;
     total += P.tiles_m * ((L.N + BN_MAX - 1) / BN_MAX);
@@ -762,7 +837,7 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
   ta.nprob = n;
   ta.total_tiles = total;
   ta.exp = g_exp.load(std::memory_order_relaxed);
-  ta.stage_out = stage_out ? 1 : 0;
+  ta.stage_out = (reserve && !rm_stage) ? 1 : 0;     // plane output through staging (never in a residual/multiplier launch)
 #ifdef BSB_TRACE
   static int trace_launch = 0, trace_sel = -2;
   if (trace_sel == -2) trace_sel = getenv("BSB_TRACE_LAUNCH") ? atoi(getenv("BSB_TRACE_LAUNCH")) : -1;
@@ -787,7 +862,9 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
     return e != cudaSuccess ? e : cudaGetLastError();
   }
   const int grid = total < sms ? total : sms;
-  if (n_planes)
+  if (rm_stage)
+    tc_grouped_linear_kernel<true, false, true><<<grid, Roles<true>::THREADS, smem_bytes<false>() + extra, s>>>(ta, maps);
+  else if (n_planes)
     tc_grouped_linear_kernel<true, false><<<grid, Roles<true>::THREADS, smem_bytes<false>() + extra, s>>>(ta, maps);
   else
     tc_grouped_linear_kernel<false, false><<<grid, Roles<false>::THREADS, smem_bytes<false>() + extra, s>>>(ta, maps);
