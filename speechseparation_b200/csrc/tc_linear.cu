@@ -529,6 +529,9 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args, const __grid_const
       // loads were), completion is counted on the warp's mbarrier; the rows are then read back conflict-free
       // (SWIZZLE_64B planes / SWIZZLE_128B boxes). No LSU global load, no dependence on L1.
       const bool ops_tma = RMS && P.ops_tma != 0;
+      // the output box shares region X with the multiplier box: the next operands are requested only after the output
+      // store has read the region (end of the step) instead of right after the operands were applied
+      const bool y_in_x = RMS && P.ops_tma != 0 && P.o_tma != 0 && P.mul != nullptr;
       auto fetch_staged = [&](int nb) {
         if (lane == 0) {
           const uint32_t bytes = ((P.Rh != nullptr || P.res != nullptr) ? 4096u : 0u) + (P.mul != nullptr ? 4096u : 0u);
@@ -621,7 +624,7 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args, const __grid_const
             v[8 * u + 6] = (v[8 * u + 6] + e3) * pm[2 * u + 1].z;
             v[8 * u + 7] = (v[8 * u + 7] + o3) * pm[2 * u + 1].w;
           }
-          if (cc + CC_STEP < ncc) { if (ops_tma) fetch_staged(nb + CC_STEP * 32); else fetch(nb + CC_STEP * 32); }
+          if (cc + CC_STEP < ncc && !y_in_x) { if (ops_tma) fetch_staged(nb + CC_STEP * 32); else fetch(nb + CC_STEP * 32); }
         } else if (has_rm) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -630,7 +633,7 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args, const __grid_const
             v[4 * j + 2] = (v[4 * j + 2] + pr[j].z) * pm[j].z;
             v[4 * j + 3] = (v[4 * j + 3] + pr[j].w) * pm[j].w;
           }
-          if (cc + CC_STEP < ncc) { if (ops_tma) fetch_staged(nb + CC_STEP * 32); else fetch(nb + CC_STEP * 32); }
+          if (cc + CC_STEP < ncc && !y_in_x) { if (ops_tma) fetch_staged(nb + CC_STEP * 32); else fetch(nb + CC_STEP * 32); }
         }
         if (args.exp & 1) { if (v[0] == 123.456f && v[31] == 1.f) orow[0] = v[5]; continue; }
         if (P.O != nullptr && P.o_tma) {
@@ -647,6 +650,10 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args, const __grid_const
           if (lane == 0) {
             tma_store_2d(&maps.o[T.pi], stg_s + Y_OFF, nb, T.m0 + q * 32);
             bulk_commit();
+          }
+          if (y_in_x && cc + CC_STEP < ncc) {
+            if (lane == 0) bulk_wait_read();
+            fetch_staged(nb + CC_STEP * 32);
           }
         } else if (orow) {
 #pragma unroll
@@ -799,8 +806,6 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
   // launches with "+ residual" / "* multiplier" operands: 3 main-loop stages + 8 KB of staging per epilogue warp
   // ([R | X or Y]); the others: 4 stages + 4 KB ([planes or Y])
   const bool rm_stage = rm && n_planes != 0 && !pair_req;
-  bool any_mul = false;
-  for (int i = 0; i < n; ++i) any_mul = any_mul || args.p[order[i]].mul != nullptr;
   const bool reserve = rm_stage || ((planes_out || rows_out) && !rm && n_planes != 0);
   const int stages = rm_stage ? 3 : Smem<false>::STAGES;
   const int stg_bytes = rm_stage ? 2 * EPI_STAGE_BYTES : EPI_STAGE_BYTES;
@@ -825,11 +830,12 @@ cudaError_t launch_tc_grouped_linear(const GroupedArgs& args, cudaStream_t s) {
     // (a TMA store moves whole 16-byte units: the extent must be a multiple of 4 floats, or run into padding the row owns;
     // in a residual/multiplier launch the output shares its staging region with the multiplier box)
     const int n4 = (L.N + 3) & ~3;
-    P.o_tma = (reserve && L.O != nullptr && n4 - L.N <= L.o_tail_pad && !(rm_stage && any_mul) &&
-               make_map_f32(&maps.o[i], L.O, L.M, n4, L.ldo)) ? 1 : 0;
     const bool has_ops = L.res != nullptr || L.mul != nullptr || L.Rp != nullptr;
     P.ops_tma = (rm_stage && has_ops && (L.res == nullptr || make_map_f32(&maps.r[i], L.res, L.M, L.N, L.ldres)) &&
                  (L.mul == nullptr || make_map_f32(&maps.m[i], L.mul, L.M, L.N, L.ldmul))) ? 1 : 0;
+    // (with a multiplier the output box reuses region X: only when that problem's operands are staged, see y_in_x)
+    P.o_tma = (reserve && L.O != nullptr && n4 - L.N <= L.o_tail_pad && !(rm_stage && L.mul != nullptr && !P.ops_tma) &&
+               make_map_f32(&maps.o[i], L.O, L.M, n4, L.ldo)) ? 1 : 0;
     P.tile_start = total;
     P.tiles_m = (L.M + tile_rows - 1) / tile_rows;
     total += P.tiles_m * ((L.N + BN_MAX - 1) / BN_MAX);
