@@ -367,8 +367,12 @@ int run_bandsplit(const float* xf, int ldx, int rows, const void* packed, float*
 }
 
 // one NormRNNResidual block (bsrnn.py:78-98) with its layout adapter (bsrnn.py:106-162)
+// feat_planes (time-axis blocks only, optional): the block's output as the A-operand planes of bandFCs_back.0 (K = 64,
+// 12 bands, kernels.cuh LstmSeq2Args::fc_planes) instead of fp32 rows; *planes_written tells whether the launch did so
+// (only the fused output Linear can).
 int run_rnn_block(int j, const float* fin, int C, int T, const void* packed, const float* st_in, float* st_out,
-                  float* fout, const Ws& w, cudaStream_t s) {
+                  float* fout, const Ws& w, cudaStream_t s, char* feat_planes = nullptr, bool* planes_written = nullptr) {
+  if (planes_written) *planes_written = false;
   const Layout& L = layout();
   const RnnBlock& R = L.rnn[j];
   const bool band = (R.ndir == 2);
@@ -417,7 +421,14 @@ int run_rnn_block(int j, const float* fin, int C, int T, const void* packed, con
       if (rows >= kTcMinRows) { a.hplanes = w.planeA; a.hp_lo = kPlaneBlock; }
       a.flags = reinterpret_cast<int*>(w.t64);                // t64 is only used by the FFMA fallback path
       a.fcw = PW(packed, R.fc.w); a.ldfcw = R.fc.Kpad; a.fcb = PW(packed, R.fc.b); a.fc_out = fout;
+      if (feat_planes != nullptr) {
+        a.fc_planes = feat_planes;
+        a.fcp_lo = kPlaneBlock;
+        a.fcp_band = w.mtiles * plane_chunks(kFeat) * (2LL * kPlaneBlock);
+        a.fc_skip_rows = 1;
+      }
       CK(launch_lstm_seq2(a, s, &fused));
+      if (planes_written) *planes_written = fused != 0 && feat_planes != nullptr;
       std::snprintf(nm, sizeof(nm), "rnn%d.rec", j);
       mark(nm, s);
     }
@@ -466,7 +477,7 @@ int run_rnn_block(int j, const float* fin, int C, int T, const void* packed, con
 
 // bandFCs_back + bandFCs_back_post + residual + x*mask (bsrnn.py:420-441)
 int run_decode(const float* feat, const float* residual, const float* xf, int ldx, int rows, const void* packed,
-               float* yf, int ldy, const Ws& w, cudaStream_t s) {
+               float* yf, int ldy, const Ws& w, cudaStream_t s, const char* feat_planes = nullptr) {
   const Layout& L = layout();
   GroupedArgs g{};
   const bool pm = use_planes(rows);
@@ -482,6 +493,11 @@ int run_decode(const float* feat, const float* residual, const float* xf, int ld
     set_prob(g.p[i], packed, L.back[i][0], feat + i * kFeat, kBands * kFeat, w.hid1 + i * kMaskHidden,
              kRealBands * kMaskHidden, rows, ACT_LRELU);
     if (pm) to_planes(g.p[i], p_b0, i);
+    if (pm && feat_planes != nullptr) {       // the last time-axis block wrote its output as this layer's A planes
+      g.p[i].Ap = feat_planes + (long long)i * w.mtiles * plane_chunks(kFeat) * (2LL * kPlaneBlock);
+      g.p[i].a_lo = kPlaneBlock;
+      g.p[i].A = nullptr;
+    }
   }
   CK(launch_grouped_linear(g, s));
   for (int i = 0; i < kRealBands; ++i) {
@@ -521,6 +537,7 @@ int run_model(const float* xf, int ldx, int C, int T, const void* packed, const 
   CKI(run_bandsplit(xf, ldx, rows, packed, residual, w.featA, w, s));
   float* fa = w.featA;
   float* fb = w.featB;
+  const char* feat_planes = nullptr;
   const long long blk = (long long)4 * C * kBands * kFeat;   // one Timewise block's (h,c) x 2 layers
   for (int j = 0; j < 4; ++j) {
     const float* si = nullptr;
@@ -529,10 +546,14 @@ int run_model(const float* xf, int ldx, int C, int T, const void* packed, const 
       if (state) si = state + (j / 2) * blk;
       if (new_state) so = new_state + (j / 2) * blk;
     }
-    CKI(run_rnn_block(j, fa, C, T, packed, si, so, fb, w, s));
+    // the last block's output goes straight to bandFCs_back.0 as planes (planeB is free from here until back.1 writes it)
+    const bool to_planes_j = j == 3 && use_planes(rows) && T >= kLstmSeqMinSteps;
+    bool wrote = false;
+    CKI(run_rnn_block(j, fa, C, T, packed, si, so, fb, w, s, to_planes_j ? w.planeB : nullptr, &wrote));
+    feat_planes = wrote ? w.planeB : nullptr;
     float* t = fa; fa = fb; fb = t;
   }
-  CKI(run_decode(fa, residual, xf, ldx, rows, packed, yf, ldy, w, s));
+  CKI(run_decode(fa, residual, xf, ldx, rows, packed, yf, ldy, w, s, feat_planes));
   return 0;
 }
 

@@ -148,6 +148,12 @@ struct LstmSeq2Args {
   const float* fcb;          // [64]
   float* fc_out;             // same addressing as x; must not alias x
   int ldfcw;
+  // optional (fused fc only): the block's output ALSO / INSTEAD as bf16 hi/lo planes in the geometry of the grouped
+  // Linear that consumes it next (LinProb::Ap with K = 64: per band [m-tile of 128 frame-rows][2 chunks][hi | lo]):
+  // band b starts fcp_band bytes after band b-1, lo = hi + fcp_lo. With fc_skip_rows the fp32 rows are not written.
+  void* fc_planes;
+  long long fcp_band, fcp_lo;
+  int fc_skip_rows;
   int fuse_fc, ngroups;      // set by the launch
   int exp;                   // timing-experiment switches (BSB_SEQ2_EXP: 1 no cell update, 2 no recurrent MMAs, 8 no x loads,
                              // 16 no h flush), 0 in production

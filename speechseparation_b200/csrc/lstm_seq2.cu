@@ -156,6 +156,11 @@ __device__ void fc_role(const LstmSeq2Args& a, int grp, uint8_t* smem_gen, uint3
       const bool ok = evalid && step < T;
       const float* res = a.x + eoff + (long long)step * a.step;
       float* dst = a.fc_out + eoff + (long long)step * a.step;
+      // plane output: sequence eg = (row c, band), frame-row rr = c * T + step -> band's block (rr / 128, chunk = half), row rr % 128
+      const long long rr = (long long)(eg / a.n_inner) * T + step;
+      const int prow = (int)(rr & 127);
+      uint8_t* pbase = reinterpret_cast<uint8_t*>(a.fc_planes) + (long long)(eg % a.n_inner) * a.fcp_band + (rr >> 7) * (4LL * kPlaneBlock);
+      uint4 ph, pl;
 #pragma unroll 1
       for (int half = 0; half < 2; ++half) {
         uint32_t v[32];
@@ -171,7 +176,19 @@ __device__ void fc_role(const LstmSeq2Args& a, int grp, uint8_t* smem_gen, uint3
             o.y = __uint_as_float(v[4 * q + 1]) + b4.y + x4.y;
             o.z = __uint_as_float(v[4 * q + 2]) + b4.z + x4.z;
             o.w = __uint_as_float(v[4 * q + 3]) + b4.w + x4.w;
-            *reinterpret_cast<float4*>(dst + half * 32 + q * 4) = o;
+            if (!a.fc_skip_rows) *reinterpret_cast<float4*>(dst + half * 32 + q * 4) = o;
+            if (a.fc_planes != nullptr) {       // two float4 = one 16-byte unit (8 bf16) of the hi and of the lo plane
+              if ((q & 1) == 0) {
+                split2(o.x, o.y, ph.x, pl.x);
+                split2(o.z, o.w, ph.y, pl.y);
+              } else {
+                split2(o.x, o.y, ph.z, pl.z);
+                split2(o.z, o.w, ph.w, pl.w);
+                uint8_t* pp = pbase + (long long)half * (2 * kPlaneBlock) + sw64(prow, q >> 1);
+                *reinterpret_cast<uint4*>(pp) = ph;
+                *reinterpret_cast<uint4*>(pp + a.fcp_lo) = pl;
+              }
+            }
           }
         }
       }
