@@ -309,16 +309,12 @@ int bsb_set_force_fp32(int on) { set_force_ffma(on); return 0; }
 namespace {
 
 // bandFCs_pre + bandFCs (bsrnn.py:404-415)
-// x_planes (optional, plane mode): the spectrum already exists as pre.0's A-operand planes in planeB (written by the
-// STFT, StftPlanes), so that the first Linear is plane-fed too
 int run_bandsplit(const float* xf, int ldx, int rows, const void* packed, float* residual, float* feat,
-                  const Ws& w, cudaStream_t s, bool x_planes = false) {
+                  const Ws& w, cudaStream_t s) {
   const Layout& L = layout();
   GroupedArgs g{};
   const bool pm = use_planes(rows);       // hidden activations as bf16 planes instead of fp32 rows
   const BandPlanes p_pre0 = band_planes(w, w.planeA, [&](int i) { return L.pre[i][0].N; });
-  const BandPlanes p_x = band_planes(w, w.planeB, [&](int i) { return kBandD[i]; });
-  if (x_planes && (!pm || residual != nullptr)) return BSB_E_ARG;     // planeB holds the residual planes in the stage API
   // residual == nullptr (fused forward, plane mode only): the residual exists as planes in planeR, which the
   // decoder reads back; otherwise fp32 rows for the caller plus planes for the next layer
   if (residual == nullptr && !pm) return BSB_E_ARG;
@@ -331,7 +327,6 @@ int run_bandsplit(const float* xf, int ldx, int rows, const void* packed, float*
   for (int i = 0; i < kRealBands; ++i) {
     set_prob(g.p[i], packed, L.pre[i][0], xf + kBandOff[i], ldx, w.bufA + kBandOff[i], kXS, rows, ACT_LRELU);
     if (pm) to_planes(g.p[i], p_pre0, i);
-    if (pm && x_planes) from_planes(g.p[i], p_x, i);
   }
   CK(launch_grouped_linear(g, s));
   // pre.2 : bufA -> residual (LReLU); the residual is needed as fp32 rows (decoder) and as the next operand
@@ -536,10 +531,10 @@ int run_decode(const float* feat, const float* residual, const float* xf, int ld
 }
 
 int run_model(const float* xf, int ldx, int C, int T, const void* packed, const float* state, float* new_state,
-              float* yf, int ldy, const Ws& w, cudaStream_t s, bool x_planes = false) {
+              float* yf, int ldy, const Ws& w, cudaStream_t s) {
   const int rows = C * T;
   float* residual = use_planes(rows) ? nullptr : w.residual;     // plane mode: the residual never exists as fp32 rows
-  CKI(run_bandsplit(xf, ldx, rows, packed, residual, w.featA, w, s, x_planes && use_planes(rows)));
+  CKI(run_bandsplit(xf, ldx, rows, packed, residual, w.featA, w, s));
   float* fa = w.featA;
   float* fb = w.featB;
   const char* feat_planes = nullptr;
@@ -688,17 +683,9 @@ int bsb_separate(const float* wav, int C, long long L, const float* window, cons
   CKI(get_ws(&w, ws, ws_bytes, (long long)C * T, true));
   cudaStream_t s = S(stream);
   marks_reset(); mark("begin", s);
-  // plane mode: the STFT writes the spectrum twice -- fp32 rows (the final "* x" needs them) and pre.0's A planes
-  const bool xp = use_planes((long long)C * T);
-  StftPlanes sp{};
-  if (xp) {
-    const BandPlanes b = band_planes(w, w.planeB, [&](int i) { return kBandD[i]; });
-    for (int i = 0; i < kRealBands; ++i) sp.base[i] = reinterpret_cast<uint8_t*>(b.band[i]);
-    sp.lo = b.lo;
-  }
-  CK(launch_stft_frames(wav, C, L, T, window, w.xf, kXS, s, xp ? &sp : nullptr));
+  CK(launch_stft_frames(wav, C, L, T, window, w.xf, kXS, s));
   mark("stft", s);
-  CKI(run_model(w.xf, kXS, C, T, packed, nullptr, nullptr, w.yf, kXS, w, s, xp));
+  CKI(run_model(w.xf, kXS, C, T, packed, nullptr, nullptr, w.yf, kXS, w, s));
   CK(launch_istft_frames(w.yf, kXS, C, T, window, out, s));
   mark("istft", s);
   return 0;

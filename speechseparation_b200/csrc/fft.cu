@@ -201,27 +201,9 @@ __device__ __forceinline__ void warp_fft1024(float2 (&v)[32], float2* tr, const 
 
 // 5 CTAs (20 warps) per SM: 96 registers with 52 bytes of spill beats 128 registers at 16 warps (88.6 -> 79.6 us at
 // cfg 2: the kernel waits on its frame loads, more resident warps hide them; 6 CTAs = 80 registers spills 400 bytes: 131 us)
-// plane geometry of the spectrum's bands (StftPlanes): first bin, 32-column chunks, valid columns of the last chunk
-__constant__ int kPlBin0[kRealBands] = {0, 1, 3, 6, 12, 24, 48, 96, 192, 384, 768};
-__constant__ int kPlNch[kRealBands] = {1, 1, 1, 1, 1, 2, 3, 6, 12, 24, 17};
-__constant__ int kPlPadBand[7] = {0, 1, 2, 3, 4, 5, 10};       // bands whose last chunk is partial ...
-__constant__ int kPlPadValid[7] = {2, 4, 6, 12, 24, 16, 2};    // ... and its valid columns
-
-// bin k (re, im) of frame-row r into the planes: band b(k) (octaves from bin 3 on), column j = 2 (k - first bin)
-__device__ __forceinline__ void plane_store_bin(const StftPlanes& P, int r, int k, float re, float im) {
-  const int b = k < 3 ? (k != 0) : min(2 + (31 - __clz(k / 3)), kRealBands - 1);
-  const int j = 2 * (k - kPlBin0[b]);
-  uint32_t hi, lo;
-  ptx::split2(re, im, hi, lo);                               // low half = column j (Re), high half = j + 1 (Im)
-  uint8_t* p = P.base[b] + ((long long)(r >> 7) * kPlNch[b] + (j >> 5)) * (2 * kPlaneBlock) + sw64(r & 127, (j & 31) >> 3) + (j & 7) * 2;
-  *reinterpret_cast<uint32_t*>(p) = hi;
-  *reinterpret_cast<uint32_t*>(p + P.lo) = lo;
-}
-
-template <bool PLANES>
 __global__ void __launch_bounds__(kFrameWarps * 32, 5)
 stft_warp_kernel(const float* __restrict__ wav, long long L, int T, int nrows, const float* __restrict__ win,
-                 const float2* __restrict__ tw, float* __restrict__ xf, int xs, const __grid_constant__ StftPlanes planes) {
+                 const float2* __restrict__ tw, float* __restrict__ xf, int xs) {
   __shared__ __align__(16) float2 tr_all[kFrameWarps][32 * kTr];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int r = blockIdx.x * kFrameWarps + warp;          // frame-row c*T + t
@@ -257,24 +239,8 @@ stft_warp_kernel(const float* __restrict__ wav, long long L, int T, int nrows, c
   warp_fft1024<false>(v, tr_all[warp], tw, lane);
   // split step: X[k] = E + W2048^k O with Z[k], Z[1024-k]; lane holds k = lane + 32 k2
   float* out = xf + (long long)r * xs;
-  if (PLANES) {
-    // zero the 16-byte units of the seven partial last chunks that hold padding; units that are partly valid are
-    // overwritten below by other lanes of this warp: __syncwarp orders the two writes
-    if (lane < 28) {
-      const int pi = lane >> 2, u = lane & 3, b = kPlPadBand[pi];
-      if (u * 8 + 8 > kPlPadValid[pi]) {
-        uint8_t* p = planes.base[b] + ((long long)(r >> 7) * kPlNch[b] + (kPlNch[b] - 1)) * (2 * kPlaneBlock) + sw64(r & 127, u);
-        *reinterpret_cast<uint4*>(p) = make_uint4(0u, 0u, 0u, 0u);
-        *reinterpret_cast<uint4*>(p + planes.lo) = make_uint4(0u, 0u, 0u, 0u);
-      }
-    }
-    __syncwarp();
-  }
   const float2 wl = __ldg(tw + kM + lane);                 // W_2048^lane
   const int partner = (32 - lane) & 31;
-  // lane part of a plane address for bins >= 96 (column 2 lane of a 64-column pair of chunks): chunk lane / 16,
-  // 16-byte unit (lane % 16) / 4 of row r % 128, 4 bytes per lane inside the unit
-  const long long pl_lane = (long long)(lane >> 4) * (2 * kPlaneBlock) + sw64(r & 127, (lane & 15) >> 2) + (lane & 3) * 4;
 #pragma unroll
   for (int k2 = 0; k2 < 32; ++k2) {
     const float2 zk = v[br5(k2)];
@@ -285,30 +251,9 @@ stft_warp_kernel(const float* __restrict__ wav, long long L, int T, int nrows, c
     const float2 e = make_float2(0.5f * (zk.x + zm.x), 0.5f * (zk.y - zm.y));
     const float2 o = make_float2(0.5f * (zk.y + zm.y), -0.5f * (zk.x - zm.x));
     const float2 wo = cmul(k2 == 0 ? wl : cmul(wl, w64(k2)), o);
-    const float2 xk = make_float2(e.x + wo.x, e.y + wo.y);
-    *reinterpret_cast<float2*>(out + 2 * k) = xk;
-    if (PLANES) {
-      if (k2 < 3) {
-        plane_store_bin(planes, r, k, xk.x, xk.y);             // bins < 96: bands change inside the warp
-      } else {
-        // bins >= 96: the 32 bins of this iteration lie in ONE band whose first bin is a multiple of 16, so band and
-        // chunk follow from the (unrolled, compile-time) k2 and the lane part of the address is loop-invariant
-        constexpr int kB0[4] = {96, 192, 384, 768};
-        const int bi = k2 < 6 ? 0 : k2 < 12 ? 1 : k2 < 24 ? 2 : 3;                 // band 7, 8, 9, 10
-        const int nch = bi == 0 ? 6 : bi == 1 ? 12 : bi == 2 ? 24 : 17;
-        const int chunk0 = 2 * k2 - kB0[bi] / 16;
-        uint32_t hi, lo;
-        ptx::split2(xk.x, xk.y, hi, lo);
-        uint8_t* p = planes.base[7 + bi] + ((long long)(r >> 7) * nch + chunk0) * (2 * kPlaneBlock) + pl_lane;
-        *reinterpret_cast<uint32_t*>(p) = hi;
-        *reinterpret_cast<uint32_t*>(p + planes.lo) = lo;
-      }
-    }
+    *reinterpret_cast<float2*>(out + 2 * k) = make_float2(e.x + wo.x, e.y + wo.y);
   }
-  if (lane == 0) {
-    *reinterpret_cast<float2*>(out + 2 * kM) = make_float2(v[0].x - v[0].y, 0.f);
-    if (PLANES) plane_store_bin(planes, r, kM, v[0].x - v[0].y, 0.f);
-  }
+  if (lane == 0) *reinterpret_cast<float2*>(out + 2 * kM) = make_float2(v[0].x - v[0].y, 0.f);
 }
 
 // A warp produces `per` consecutive 1024-sample output blocks of one row; the windowed second
@@ -581,14 +526,10 @@ const float2* twiddle_tables(cudaStream_t, cudaError_t* err) {
   }
 
 cudaError_t launch_stft_frames(const float* wav, int C, long long L, int T, const float* window,
-                               float* xf, int xs, cudaStream_t s, const StftPlanes* planes) {
+                               float* xf, int xs, cudaStream_t s) {
   BSB_TABLES(window, tw);
   const int nrows = C * T;
-  const int grid = (nrows + kFrameWarps - 1) / kFrameWarps;
-  if (planes != nullptr)
-    stft_warp_kernel<true><<<grid, kFrameWarps * 32, 0, s>>>(wav, L, T, nrows, window, tw, xf, xs, *planes);
-  else
-    stft_warp_kernel<false><<<grid, kFrameWarps * 32, 0, s>>>(wav, L, T, nrows, window, tw, xf, xs, StftPlanes{});
+  stft_warp_kernel<<<(nrows + kFrameWarps - 1) / kFrameWarps, kFrameWarps * 32, 0, s>>>(wav, L, T, nrows, window, tw, xf, xs);
   count_launch();
   return cudaGetLastError();
 }
@@ -719,8 +660,8 @@ cudaError_t launch_stft_pack_static(const float* wav, int C, long long L, int T,
   cudaError_t e = static_setup(&p);
   if (e != cudaSuccess) return e;
   const int nrows = C * T;
-  stft_warp_kernel<false><<<(nrows + kFrameWarps - 1) / kFrameWarps, kFrameWarps * 32, 0, s>>>(
-      wav, L, T, nrows, window ? window : p->window, p->tw, p->scratch, kXS, StftPlanes{});
+  stft_warp_kernel<<<(nrows + kFrameWarps - 1) / kFrameWarps, kFrameWarps * 32, 0, s>>>(
+      wav, L, T, nrows, window ? window : p->window, p->tw, p->scratch, kXS);
   count_launch();
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   dim3 grid((T + 31) / 32, (kSpec + 31) / 32, C);

@@ -171,16 +171,9 @@ int force_ffma();
 // ------------------------------------------------------------------------------------
 // signal kernels
 // ------------------------------------------------------------------------------------
-// optional second output of the STFT: the spectrum ALSO as the A-operand planes of bandFCs_pre.0 (LinProb::Ap geometry
-// with K = d_i: per band [m-tile of 128 frame-rows][chunk of 32 columns][hi | lo][128 x 64 B, SWIZZLE_64B], partial last
-// chunks zero padded), so that the first Linear is plane-fed like the rest
-struct StftPlanes {
-  uint8_t* base[kRealBands];
-  long long lo;                 // bytes from a hi plane to its lo plane
-};
 // wav[C][L] -> xf[C*T][xs] (frame-major, 2050 valid floats), torch.stft(center=True, reflect)
 cudaError_t launch_stft_frames(const float* wav, int C, long long L, int T, const float* window,
-                               float* xf, int xs, cudaStream_t s, const StftPlanes* planes = nullptr);
+                               float* xf, int xs, cudaStream_t s);
 // xf[C*T][xs] -> wav[C][1024*(T-1)], torch.istft semantics
 cudaError_t launch_istft_frames(const float* xf, int xs, int C, int T, const float* window,
                                 float* wav, cudaStream_t s);
