@@ -573,14 +573,13 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args, const __grid_const
         __syncwarp();                        // every lane has read: the regions may be refilled
       };
       const bool has_rm = P.res != nullptr || P.mul != nullptr || P.Rh != nullptr;      // warp-uniform
-      int cc = ew >> 2;
+      int cc = (args.exp & 2) ? ncc : (ew >> 2);     // (timing experiment 2: no epilogue work at all, so no operand request either)
       if (has_rm && cc < ncc) { if (ops_tma) fetch_staged(T.n0 + cc * 32); else fetch(T.n0 + cc * 32); }
       if (lane == 0) mbar_wait(smem_u32(&bar_tfull[acc]), acc_phase);
       __syncwarp();
       if (ew == BSB_TRACE_EPI && lane == 0) TRACE(2, 20);
       tc_fence_after();
       const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN_MAX);
-      if (args.exp & 2) cc = ncc;
       for (; cc < ncc; cc += CC_STEP) {
         const int nb = T.n0 + cc * 32;
         uint32_t r[32];
@@ -635,7 +634,11 @@ tc_grouped_linear_kernel(const __grid_constant__ TcArgs args, const __grid_const
           }
           if (cc + CC_STEP < ncc && !y_in_x) { if (ops_tma) fetch_staged(nb + CC_STEP * 32); else fetch(nb + CC_STEP * 32); }
         }
-        if (args.exp & 1) { if (v[0] == 123.456f && v[31] == 1.f) orow[0] = v[5]; continue; }
+        if (args.exp & 1) {                 // timing experiment: no split, no stores (the deferred operand request still has to happen)
+          if (v[0] == 123.456f && v[31] == 1.f) orow[0] = v[5];
+          if (y_in_x && cc + CC_STEP < ncc) fetch_staged(nb + CC_STEP * 32);
+          continue;
+        }
         if (P.O != nullptr && P.o_tma) {
           // fp32 rows through the staging buffer ([32 rows][128 B], SWIZZLE_128B: unit j of row r at j ^ (r & 7)) and
           // ONE 2-D TMA store of the 32 x 32 box; rows >= M / columns >= N are clipped by the hardware
